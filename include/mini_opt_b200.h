@@ -1,0 +1,162 @@
+/*
+ * mini_opt_b200 — C ABI of the batched B200 solver for mini_opt's hot path.
+ *
+ * The reference (gareth-cross/mini_opt) has no FFI: its boundary is the C++ class surface
+ *   QPInteriorPointSolver::Setup/Solve            include/mini_opt/qp.hpp:167-205, source/qp.cc:20-151
+ *   QPInteriorPointSolver::Iterate (private)      source/qp.cc:153-201
+ *   ConstrainedNonlinearLeastSquares::LinearizeAndFillQP / Solve   source/nonlinear.cc:75-214
+ * Every entry point below names the reference function it replaces. Conventions:
+ *   - plain C structs, caller-owned buffers, no exceptions; `int` return (MO_OK or a negative mo_error);
+ *   - per-problem numerical trouble never aborts a batch: it is reported in `status[i]`;
+ *   - unless the name ends in `_host`, every data pointer is a DEVICE pointer valid on `device`,
+ *     and the call is asynchronous on `cuda_stream` (a `cudaStream_t`, NULL = legacy default stream);
+ *   - all floating point data is IEEE fp64; matrices are column-major like Eigen::MatrixXd.
+ */
+#ifndef MINI_OPT_B200_H_
+#define MINI_OPT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MO_ABI_VERSION 1
+
+/* ---- return codes of the entry points (not per-problem status) ---- */
+typedef enum mo_error {
+  MO_OK = 0,
+  MO_ERR_INVALID_ARGUMENT = -1, /* NULL where data is required, negative dims, constraint index out of range */
+  MO_ERR_INVALID_PARAMS = -2,   /* the reference's CheckParams would have thrown (qp.cc:76-82, nonlinear.cc:49-73) */
+  MO_ERR_UNSUPPORTED_SHAPE = -3,/* problem too large for every kernel variant (shared memory) */
+  MO_ERR_CUDA = -4,             /* a CUDA runtime call failed; see mo_last_error_string() */
+  MO_ERR_NO_DEVICE = -5         /* no CUDA device / wrong architecture (needs sm_100) */
+} mo_error;
+
+/* ---- per-problem termination status of the interior point solve ----
+ * 0/1 are QPInteriorPointTerminationState (include/mini_opt/structs.hpp:97-102).
+ * 2 replaces the FailedFactorization exception (source/qp.cc:303-307) and
+ * 3 replaces F_ASSERT(all s > 0) (source/qp.cc:285): a batch cannot throw per problem. */
+enum {
+  MO_QP_SATISFIED_KKT_TOL = 0,
+  MO_QP_MAX_ITERATIONS = 1,
+  MO_QP_FAILED_FACTORIZATION = 2,
+  MO_QP_NONPOSITIVE_SLACK = 3
+};
+
+/* BarrierStrategy, include/mini_opt/structs.hpp:24-31 */
+enum { MO_BARRIER_COMPLEMENTARITY = 0, MO_BARRIER_FIXED_DECREASE = 1, MO_BARRIER_PREDICTOR_CORRECTOR = 2 };
+/* InitialGuessMethod, include/mini_opt/structs.hpp:34-41 */
+enum { MO_GUESS_NAIVE = 0, MO_GUESS_SOLVE_EQUALITY_CONSTRAINED = 1, MO_GUESS_USER_PROVIDED = 2 };
+
+/* flags of mo_qp_batch */
+enum {
+  /* Caller promises m == 2n and constraint 2i is (i,+1,b), constraint 2i+1 is (i,-1,b), i.e.
+   * Var(i) >= lo_i, Var(i) <= hi_i with ineq_b = {-lo_0, hi_0, -lo_1, hi_1, ...}. ineq_var / ineq_a
+   * are then not read (may be NULL). This is the box layout of BASELINE configs 2-5. */
+  MO_QP_FLAG_BOX_PAIRS = 1
+};
+
+/*
+ * A batch of QPs of uniform shape (struct QP, include/mini_opt/qp.hpp:104-124):
+ *    minimise 1/2 x'Gx + c'x   s.t.  A_eq x + b_eq = 0,   a_i * x[var_i] + b_i >= 0.
+ * Problem p occupies [p*stride, (p+1)*stride) of each array.
+ */
+typedef struct mo_qp_batch {
+  int32_t n;              /* variables per problem (N)               */
+  int32_t k;              /* equality rows per problem (K), may be 0 */
+  int32_t m;              /* inequality slots per problem (M), may be 0 */
+  int32_t flags;          /* MO_QP_FLAG_*                            */
+  int64_t batch;          /* number of problems                      */
+  const double* G;        /* [batch][n*n] column-major; only the lower triangle is read (qp.cc:289,404) */
+  const double* c;        /* [batch][n]                              */
+  const double* A_eq;     /* [batch][k*n] column-major k x n (NULL if k == 0) */
+  const double* b_eq;     /* [batch][k]                              */
+  const int32_t* ineq_var;/* [batch][m] LinearInequalityConstraint::variable (qp.hpp:28-35) */
+  const double* ineq_a;   /* [batch][m]                              */
+  const double* ineq_b;   /* [batch][m]                              */
+  const int32_t* ineq_count; /* optional [batch]: problem p uses only its first ineq_count[p] <= m slots
+                                (ragged batches such as GenerateRandomQP, test/qp_test.cc:483-524). NULL = m. */
+} mo_qp_batch;
+
+/* QPInteriorPointSolver::Params, include/mini_opt/qp.hpp:134-164 (same defaults via mo_qp_params_default). */
+typedef struct mo_qp_params {
+  double initial_mu;
+  double sigma;
+  double termination_kkt_tol;
+  double termination_complementarity_tol;
+  int32_t max_iterations;
+  int32_t barrier_strategy;
+  int32_t decrease_mu_only_on_small_error;
+  int32_t initial_guess_method;
+  int32_t initialize_mu_with_complementarity;
+  int32_t reserved;
+} mo_qp_params;
+
+#define MO_QP_ITER_LOG_STRIDE 14
+/* One row of iter_log = QPInteriorPointIteration (include/mini_opt/structs.hpp:81-94):
+ *  [0..3]  kkt_initial {r_dual, r_comp, r_primal_eq, r_primal_ineq}
+ *  [4..7]  kkt_final   {same}
+ *  [8]     ip_outputs.mu   [9] alpha.primal [10] alpha.dual
+ *  [11]    alpha_probe.primal [12] alpha_probe.dual [13] mu_affine   (NaN unless PREDICTOR_CORRECTOR) */
+
+typedef struct mo_qp_out {
+  double* vars;      /* [batch][n+2m+k] = [x | s | y | z] (qp.cc:548-582). In/out for MO_GUESS_USER_PROVIDED. */
+  int32_t* status;   /* [batch] MO_QP_*                                                  */
+  int32_t* iters;    /* [batch] == outputs.iterations.size()                             */
+  double* kkt_final; /* optional [batch][4]: kkt_final of the last iteration              */
+  double* lagrange;  /* optional [batch][2]: {min y, ||y||_inf} (qp.cc:539-546); NaN if k == 0 */
+  double* iter_log;  /* optional [batch][max_iterations][MO_QP_ITER_LOG_STRIDE]           */
+} mo_qp_out;
+
+/* Fills *p with the reference defaults (qp.hpp:136-163). */
+void mo_qp_params_default(mo_qp_params* p);
+
+/* Elements of `vars` per problem: n + 2m + k. */
+int64_t mo_qp_vars_stride(int32_t n, int32_t k, int32_t m);
+
+/*
+ * Replaces: QPInteriorPointSolver::Setup + Solve for every problem of the batch
+ * (source/qp.cc:20-73, :100-151; ComputeInitialGuess :439-482).
+ * Device pointers, asynchronous on `cuda_stream`.
+ */
+int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
+                         int device, void* cuda_stream);
+
+/*
+ * Same contract with HOST pointers: stages through pinned memory, H2D, solve, D2H, synchronises
+ * before returning. This is the call a host-side user of the reference makes (data lives in Eigen
+ * objects on the host) and what bench.py's `e2e` times.
+ */
+int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
+                              int device);
+
+/*
+ * Replaces: one call of QPInteriorPointSolver::Iterate(mu, strategy) (source/qp.cc:153-201) on
+ * caller-provided state `vars` [batch][n+2m+k] (updated in place). Used for step-level parity with
+ * the reference's Elimination tests (test/qp_test.cc:101-241).
+ *   delta_out     optional [batch][n+2m+k]: the Newton direction [dx|ds|dy|dz] before scaling by alpha
+ *   ip_out        optional [batch][6]: {mu, alpha.primal, alpha.dual, alpha_probe.primal, alpha_probe.dual, mu_affine}
+ *   kkt_out       optional [batch][4]: KKT error norms (ComputeErrors(mu), qp.cc:423-437) AFTER the step
+ *   status        [batch]: MO_QP_SATISFIED_KKT_TOL (0) if the step was taken, MO_QP_FAILED_FACTORIZATION /
+ *                 MO_QP_NONPOSITIVE_SLACK otherwise (state untouched)
+ */
+int mo_qp_ip_newton_step_batch(const mo_qp_batch* problems, double mu, int32_t barrier_strategy,
+                               double* vars, double* delta_out, double* ip_out, double* kkt_out,
+                               int32_t* status, int device, void* cuda_stream);
+
+/* Name of the kernel variant mo_qp_ip_solve_batch would launch for this shape ("warp16", "cta", ...). */
+const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags);
+
+/* Number of kernel launches issued by this library since load (bench.py's gpu_launches). */
+int64_t mo_kernel_launch_count(void);
+
+/* Human-readable description of the last MO_ERR_CUDA in this thread. */
+const char* mo_last_error_string(void);
+
+int mo_abi_version(void);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+#endif /* MINI_OPT_B200_H_ */

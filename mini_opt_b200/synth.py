@@ -1,0 +1,90 @@
+"""Seeded synthetic batches for BASELINE configs 2/4/5.
+
+Recipe per problem: ``A ~ U(-1,1)^{n x n}``, ``G = A'A + 0.1 n I``, ``c ~ 4 U(-1,1)``, ``A_eq ~ U(-1,1)^{k x n}``,
+``b_eq ~ 0.1 U(-1,1)``, box ``-1 <= x_i <= 1`` stored as the interleaved pairs ``(i,+1,1), (i,-1,1)``
+(``MO_QP_FLAG_BOX_PAIRS``: constraint 2i is ``Var(i) >= -1``, 2i+1 is ``Var(i) <= 1``).
+
+The same bytes are fed to the reference / oracle and to the CUDA path. Two generators with the same recipe:
+numpy (tests, golden fixtures) and torch (bench: generates directly in HBM). They do NOT produce the same
+stream; parity never compares across generators.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import abi
+
+
+def box_qp_batch_numpy(n: int, k: int, batch: int, seed: int = 1234, explicit_constraints: bool = True
+                       ) -> abi.QPBatchArrays:
+    rng = np.random.default_rng(seed)
+    A = rng.uniform(-1.0, 1.0, size=(batch, n, n))
+    G = np.einsum("bji,bjk->bik", A, A) + 0.1 * n * np.eye(n)[None]
+    G = 0.5 * (G + G.transpose(0, 2, 1))
+    c = 4.0 * rng.uniform(-1.0, 1.0, size=(batch, n))
+    A_eq = rng.uniform(-1.0, 1.0, size=(batch, k, n)) if k else None
+    b_eq = 0.1 * rng.uniform(-1.0, 1.0, size=(batch, k)) if k else None
+    m = 2 * n
+    ineq_b = np.ones((batch, m))
+    arrs = abi.QPBatchArrays(
+        n=n, k=k, m=m, batch=batch,
+        G=np.ascontiguousarray(G), c=np.ascontiguousarray(c),
+        A_eq=np.ascontiguousarray(A_eq.transpose(0, 2, 1)) if k else None,  # column-major k x n
+        b_eq=np.ascontiguousarray(b_eq) if k else None,
+        ineq_b=ineq_b, flags=abi.MO_QP_FLAG_BOX_PAIRS)
+    if explicit_constraints:
+        var = np.repeat(np.arange(n, dtype=np.int32), 2)
+        a = np.tile(np.array([1.0, -1.0]), n)
+        arrs.ineq_var = np.ascontiguousarray(np.broadcast_to(var, (batch, m)))
+        arrs.ineq_a = np.ascontiguousarray(np.broadcast_to(a, (batch, m)))
+    return arrs
+
+
+def box_qp_batch_torch(n: int, k: int, batch: int, seed: int, device, chunk: int = 1 << 18) -> abi.QPBatchArrays:
+    """Same recipe, generated on ``device`` in chunks (bounded scratch memory)."""
+    import torch
+
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    f64 = dict(dtype=torch.float64, device=device)
+    m = 2 * n
+    G = torch.empty((batch, n, n), **f64)
+    c = torch.empty((batch, n), **f64)
+    A_eq = torch.empty((batch, n, k), **f64) if k else None
+    b_eq = torch.empty((batch, k), **f64) if k else None
+    eye = 0.1 * n * torch.eye(n, **f64)
+    for lo in range(0, batch, chunk):
+        hi = min(batch, lo + chunk)
+        A = torch.rand((hi - lo, n, n), generator=gen, **f64) * 2 - 1
+        Gc = torch.bmm(A.transpose(1, 2), A) + eye
+        G[lo:hi] = 0.5 * (Gc + Gc.transpose(1, 2))
+        c[lo:hi] = 4.0 * (torch.rand((hi - lo, n), generator=gen, **f64) * 2 - 1)
+        if k:
+            A_eq[lo:hi] = torch.rand((hi - lo, n, k), generator=gen, **f64) * 2 - 1
+            b_eq[lo:hi] = 0.1 * (torch.rand((hi - lo, k), generator=gen, **f64) * 2 - 1)
+    ineq_b = torch.ones((batch, m), **f64)
+    return abi.QPBatchArrays(n=n, k=k, m=m, batch=batch, G=G, c=c, A_eq=A_eq, b_eq=b_eq, ineq_b=ineq_b,
+                             flags=abi.MO_QP_FLAG_BOX_PAIRS)
+
+
+def to_numpy(arrs: abi.QPBatchArrays, lo: int = 0, hi: int | None = None) -> abi.QPBatchArrays:
+    """Host copy of problems [lo, hi) of a (possibly device-resident torch) batch."""
+    hi = arrs.batch if hi is None else hi
+
+    def conv(t):
+        if t is None:
+            return None
+        s = t[lo:hi]
+        return np.ascontiguousarray(s.cpu().numpy() if hasattr(s, "cpu") else s)
+
+    return abi.QPBatchArrays(n=arrs.n, k=arrs.k, m=arrs.m, batch=hi - lo, G=conv(arrs.G), c=conv(arrs.c),
+                             A_eq=conv(arrs.A_eq), b_eq=conv(arrs.b_eq), ineq_var=conv(arrs.ineq_var),
+                             ineq_a=conv(arrs.ineq_a), ineq_b=conv(arrs.ineq_b),
+                             ineq_count=conv(arrs.ineq_count), flags=arrs.flags)
+
+
+def solve_params(guess: int = abi.MO_GUESS_SOLVE_EQUALITY_CONSTRAINED) -> abi.QPParams:
+    """The ``ComputeStepDirection`` configuration (source/nonlinear.cc:226-239) used by SURVEY §8(d)."""
+    return abi.QPParams(initial_mu=1.0, sigma=0.1, termination_kkt_tol=1e-9, termination_complementarity_tol=1e-6,
+                        max_iterations=30, barrier_strategy=abi.MO_BARRIER_COMPLEMENTARITY,
+                        initial_guess_method=guess)

@@ -1,0 +1,136 @@
+"""TEST INFRASTRUCTURE — loader for the CPU checkers. Never imported by the product package.
+
+* ``liboracle.so``            plain-C restatement of the reference algorithm (oracle/*.c)
+* ``_ref/libminiopt_ref.so``  the unmodified reference compiled from /root/reference + extern "C" harness
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs
+may import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+from mini_opt_b200 import abi
+
+HERE = Path(__file__).resolve().parent
+ORACLE_SO = HERE / "liboracle.so"
+REF_SO = HERE / "_ref" / "libminiopt_ref.so"
+REFERENCE_ROOT = Path(os.environ.get("MINI_OPT_REFERENCE", "/root/reference"))
+
+
+def build(verbose: bool = False) -> None:
+    """Compile the C restatement and, when the reference sources are present, oracle/_ref."""
+    cmd = ["make", "-C", str(HERE), f"REF={REFERENCE_ROOT}", "-j8", "all"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout[-4000:], res.stderr[-4000:])
+    if res.returncode != 0:
+        raise RuntimeError("oracle build failed")
+
+
+_oracle = None
+_ref = None
+
+
+def _bind_qp(lib, prefix: str, with_threads: bool):
+    solve = getattr(lib, f"{prefix}_qp_solve_batch")
+    solve.restype = C.c_int64
+    solve.argtypes = [C.POINTER(abi.MoQpBatch), C.POINTER(abi.MoQpParams), C.POINTER(abi.MoQpOut)] + (
+        [C.c_int] if with_threads else [])
+    step = getattr(lib, f"{prefix}_qp_newton_step_batch")
+    step.restype = C.c_int
+    step.argtypes = [C.POINTER(abi.MoQpBatch), C.c_double, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                     C.c_void_p, C.c_void_p]
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        if not ORACLE_SO.exists():
+            build()
+        _oracle = C.CDLL(str(ORACLE_SO))
+        _bind_qp(_oracle, "oracle", with_threads=False)
+    return _oracle
+
+
+def ref_available() -> bool:
+    return REF_SO.exists() or (REFERENCE_ROOT / "source" / "qp.cc").exists()
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        if not REF_SO.exists():
+            build()
+        _ref = C.CDLL(str(REF_SO))
+        _bind_qp(_ref, "ref", with_threads=True)
+        _ref.ref_generate_random_qp.restype = C.c_int
+        _ref.ref_generate_random_qp.argtypes = [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 6
+        _ref.ref_hardware_concurrency.restype = C.c_int
+    return _ref
+
+
+def _check_host(arrs: abi.QPBatchArrays):
+    for name in ("G", "c", "A_eq", "b_eq", "ineq_var", "ineq_a", "ineq_b", "ineq_count"):
+        a = getattr(arrs, name)
+        if a is not None:
+            assert isinstance(a, np.ndarray) and a.flags["C_CONTIGUOUS"], name
+
+
+def qp_solve(which: str, arrs: abi.QPBatchArrays, params: abi.QPParams, log: bool = False, nthreads: int = 1,
+             user_vars: np.ndarray | None = None):
+    """Solve a HOST batch with the C restatement (``which='oracle'``) or the reference (``'ref'``).
+
+    Returns (QPOutArrays of numpy arrays, total Newton steps).
+    """
+    _check_host(arrs)
+    out = abi.alloc_out_numpy(arrs.batch, arrs.n, arrs.k, arrs.m, params.max_iterations, log)
+    if user_vars is not None:
+        out.vars[...] = user_vars
+    b, p, o = arrs.to_c(), params.to_c(), out.to_c()
+    if which == "oracle":
+        total = oracle_lib().oracle_qp_solve_batch(C.byref(b), C.byref(p), C.byref(o))
+    elif which == "ref":
+        total = ref_lib().ref_qp_solve_batch(C.byref(b), C.byref(p), C.byref(o), int(nthreads))
+    else:
+        raise ValueError(which)
+    if total < 0:
+        raise RuntimeError(f"{which}_qp_solve_batch failed: {total}")
+    return out, int(total)
+
+
+def qp_newton_step(which: str, arrs: abi.QPBatchArrays, mu: float, strategy: int, vars_in: np.ndarray):
+    """One ``Iterate(mu, strategy)`` per problem. Returns dict(vars, delta, ip, kkt, status)."""
+    _check_host(arrs)
+    B, stride = arrs.batch, abi.vars_stride(arrs.n, arrs.k, arrs.m)
+    v = np.ascontiguousarray(vars_in, dtype=np.float64).reshape(B, stride).copy()
+    delta = np.zeros((B, stride))
+    ip = np.zeros((B, 6))
+    kkt = np.zeros((B, 4))
+    status = np.full(B, -1, dtype=np.int32)
+    b = arrs.to_c()
+    fn = oracle_lib().oracle_qp_newton_step_batch if which == "oracle" else ref_lib().ref_qp_newton_step_batch
+    rc = fn(C.byref(b), float(mu), int(strategy), v.ctypes.data, delta.ctypes.data, ip.ctypes.data,
+            kkt.ctypes.data, status.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"{which} newton step failed: {rc}")
+    return dict(vars=v, delta=delta, ip=ip, kkt=kkt, status=status)
+
+
+def generate_random_qp(seed: int, dim: int = 8, p_inequality: float = 0.5):
+    """The reference's own ``GenerateRandomQP`` (test/qp_test.cc:483-524). Needs oracle/_ref."""
+    lib = ref_lib()
+    G = np.zeros((dim, dim))
+    c = np.zeros(dim)
+    var = np.zeros(dim, dtype=np.int32)
+    a = np.zeros(dim)
+    b = np.zeros(dim)
+    sol = np.zeros(dim)
+    cnt = lib.ref_generate_random_qp(int(seed), int(dim), float(p_inequality), G.ctypes.data, c.ctypes.data,
+                                     var.ctypes.data, a.ctypes.data, b.ctypes.data, sol.ctypes.data)
+    return dict(G=G, c=c, var=var[:cnt].copy(), a=a[:cnt].copy(), b=b[:cnt].copy(), solution=sol, count=cnt)
