@@ -15,6 +15,7 @@
 #ifndef MINI_OPT_B200_H_
 #define MINI_OPT_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -131,6 +132,11 @@ int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params
 int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
                               int device);
 
+/* Pinned (page-locked) host memory: buffers allocated here are DMA'd directly by the *_host entry points;
+ * pageable buffers work too but are staged by the driver. */
+void* mo_host_alloc(size_t bytes);
+void mo_host_free(void* p);
+
 /*
  * Replaces: one call of QPInteriorPointSolver::Iterate(mu, strategy) (source/qp.cc:153-201) on
  * caller-provided state `vars` [batch][n+2m+k] (updated in place). Used for step-level parity with
@@ -153,6 +159,10 @@ int64_t mo_kernel_launch_count(void);
 
 /* Human-readable description of the last MO_ERR_CUDA in this thread. */
 const char* mo_last_error_string(void);
+
+/* Measures this GPU's FP64 FMA peak (dependent-free DFMA streams, CUDA events, best of 5) in TFLOP/s: the
+ * roofline denominator for the FP64-bound kernels (bench.py). Synchronous. */
+int mo_measure_fp64_peak(int device, double* tflops_out);
 
 int mo_abi_version(void);
 

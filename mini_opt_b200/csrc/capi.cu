@@ -1,0 +1,442 @@
+// C ABI of mini_opt_b200 (include/mini_opt_b200.h): argument checking, kernel selection, launches,
+// and the host-buffer convenience entry point. No torch, no Eigen: plain CUDA runtime.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "qp_generic.cuh"
+#include "qp_tpp.cuh"
+
+namespace {
+
+thread_local std::string g_last_error;
+std::atomic<long long> g_launches{0};
+
+int cuda_fail(cudaError_t e, const char* what) {
+  g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
+  return MO_ERR_CUDA;
+}
+#define MO_CUDA(call)                                  \
+  do {                                                 \
+    cudaError_t e_ = (call);                           \
+    if (e_ != cudaSuccess) return cuda_fail(e_, #call); \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) return;
+    ok = (prev == dev) || cudaSetDevice(dev) == cudaSuccess;
+    if (prev == dev) prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct DeviceInfo {
+  bool queried = false;
+  int sms = 0, cc_major = 0, max_smem_optin = 0;
+};
+DeviceInfo g_dev[64];
+std::mutex g_dev_mu;
+
+int device_info(int dev, DeviceInfo* out) {
+  if (dev < 0 || dev >= 64) { g_last_error = "device index out of range"; return MO_ERR_NO_DEVICE; }
+  std::lock_guard<std::mutex> lk(g_dev_mu);
+  DeviceInfo& d = g_dev[dev];
+  if (!d.queried) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || dev >= count) {
+      cudaGetLastError();
+      g_last_error = "no CUDA device " + std::to_string(dev);
+      return MO_ERR_NO_DEVICE;
+    }
+    MO_CUDA(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev));
+    MO_CUDA(cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+    MO_CUDA(cudaDeviceGetAttribute(&d.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    d.queried = true;
+  }
+  if (d.cc_major != 10) {
+    g_last_error = "mini_opt_b200 kernels are built for sm_100a only; device has compute capability major " +
+                   std::to_string(d.cc_major);
+    return MO_ERR_NO_DEVICE;
+  }
+  *out = d;
+  return MO_OK;
+}
+
+// CheckParams, qp.cc:76-82
+int check_params(const mo_qp_params* p) {
+  if (!(p->initial_mu > 0) || !(p->sigma > 0) || !(p->sigma <= 1.0) || !(p->termination_kkt_tol > 0) ||
+      !(p->max_iterations > 0))
+    return MO_ERR_INVALID_PARAMS;
+  if (p->barrier_strategy < 0 || p->barrier_strategy > 2 || p->initial_guess_method < 0 || p->initial_guess_method > 2)
+    return MO_ERR_INVALID_PARAMS;
+  return MO_OK;
+}
+
+int check_batch(const mo_qp_batch* b) {
+  if (!b || b->n <= 0 || b->k < 0 || b->m < 0 || b->batch < 0) return MO_ERR_INVALID_ARGUMENT;
+  if (b->batch == 0) return MO_OK;
+  if (!b->G || !b->c) return MO_ERR_INVALID_ARGUMENT;
+  if (b->k > 0 && (!b->A_eq || !b->b_eq)) return MO_ERR_INVALID_ARGUMENT;
+  if (b->m > 0) {
+    if (!b->ineq_b) return MO_ERR_INVALID_ARGUMENT;
+    if (b->flags & MO_QP_FLAG_BOX_PAIRS) {
+      if (b->m != 2 * b->n) return MO_ERR_INVALID_ARGUMENT;
+    } else if (!b->ineq_var || !b->ineq_a) {
+      return MO_ERR_INVALID_ARGUMENT;
+    }
+  }
+  return MO_OK;
+}
+
+mo::QPArgs make_args(const mo_qp_batch* b, const mo_qp_params* p, const mo_qp_out* o) {
+  mo::QPArgs a{};
+  a.n = b->n; a.k = b->k; a.m = b->m; a.flags = b->flags; a.batch = b->batch;
+  a.G = b->G; a.c = b->c; a.A = b->A_eq; a.b = b->b_eq;
+  a.ivar = b->ineq_var; a.ia = b->ineq_a; a.ib = b->ineq_b; a.icount = b->ineq_count;
+  if (p) {
+    a.initial_mu = p->initial_mu; a.sigma = p->sigma; a.kkt_tol = p->termination_kkt_tol;
+    a.comp_tol = p->termination_complementarity_tol; a.max_iterations = p->max_iterations;
+    a.strategy = p->barrier_strategy; a.decrease_mu_only_on_small_error = p->decrease_mu_only_on_small_error;
+    a.guess = p->initial_guess_method; a.init_mu_with_comp = p->initialize_mu_with_complementarity;
+  }
+  if (o) {
+    a.vars = o->vars; a.status = o->status; a.iters = o->iters; a.kkt_final = o->kkt_final;
+    a.lagrange = o->lagrange; a.iter_log = o->iter_log;
+  }
+  return a;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// kernel selection
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kTppWarpsPerBlock = 4;
+constexpr int kTppMinBlocks = 2;
+
+// (N, K) shapes with a thread-per-problem instantiation (box pairs, m == 2n, uniform count).
+#define MO_TPP_SHAPES(X) X(8, 2) X(8, 0) X(4, 1)
+
+template <int N, int K>
+int launch_tpp(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
+  using L = mo::TppLayout<N, K>;
+  constexpr int threads = 32 * kTppWarpsPerBlock;
+  auto kernel = mo::qp_ip_tpp_kernel<N, K, kTppWarpsPerBlock, kTppMinBlocks>;
+  const size_t smem = sizeof(double) * L::E * (threads + 1);
+  static thread_local int configured_dev = -1;
+  static thread_local int blocks_per_sm = 0;
+  int cur = 0;
+  MO_CUDA(cudaGetDevice(&cur));
+  if (configured_dev != cur) {
+    MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, threads, smem));
+    if (blocks_per_sm < 1) { g_last_error = "tpp kernel does not fit on an SM"; return MO_ERR_UNSUPPORTED_SHAPE; }
+    configured_dev = cur;
+  }
+  const long long want = (a.batch + threads - 1) / threads;
+  const long long cap = (long long)dev.sms * blocks_per_sm;
+  const int grid = (int)(want < cap ? want : cap);
+  kernel<<<grid, threads, smem, stream>>>(a);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+bool tpp_eligible(int n, int k, int m, int flags, bool ragged, int strategy) {
+  if (!(flags & MO_QP_FLAG_BOX_PAIRS) || ragged || m != 2 * n) return false;
+  if (strategy == MO_BARRIER_PREDICTOR_CORRECTOR) return false;
+#define X(N_, K_) if (n == N_ && k == K_) return true;
+  MO_TPP_SHAPES(X)
+#undef X
+  return false;
+}
+
+int generic_threads(int n, int k) {
+  const int p = n + k;
+  return p <= 32 ? 32 : (p <= 64 ? 128 : 256);
+}
+
+template <int THREADS>
+int launch_generic(const mo::QPArgs& a, const mo::StepArgs* step, const DeviceInfo& dev, cudaStream_t stream) {
+  const size_t smem = sizeof(double) * mo::gen_smem_doubles(a.n, a.k, a.m, THREADS);
+  if (smem > (size_t)dev.max_smem_optin) {
+    g_last_error = "problem too large for shared memory: needs " + std::to_string(smem) + " bytes";
+    return MO_ERR_UNSUPPORTED_SHAPE;
+  }
+  int bps = 0;
+  if (step) {
+    auto kernel = mo::qp_ip_generic_step_kernel<THREADS>;
+    MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, THREADS, smem));
+    const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
+    const int grid = (int)(a.batch < cap ? a.batch : cap);
+    kernel<<<grid, THREADS, smem, stream>>>(a, *step);
+  } else {
+    auto kernel = mo::qp_ip_generic_kernel<THREADS>;
+    MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, THREADS, smem));
+    const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
+    const int grid = (int)(a.batch < cap ? a.batch : cap);
+    kernel<<<grid, THREADS, smem, stream>>>(a);
+  }
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+int dispatch_generic(const mo::QPArgs& a, const mo::StepArgs* step, const DeviceInfo& dev, cudaStream_t stream) {
+  switch (generic_threads(a.n, a.k)) {
+    case 32: return launch_generic<32>(a, step, dev, stream);
+    case 128: return launch_generic<128>(a, step, dev, stream);
+    default: return launch_generic<256>(a, step, dev, stream);
+  }
+}
+
+int dispatch_solve(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
+  if (tpp_eligible(a.n, a.k, a.m, a.flags, a.icount != nullptr, a.strategy)) {
+#define X(N_, K_) if (a.n == N_ && a.k == K_) return launch_tpp<N_, K_>(a, dev, stream);
+    MO_TPP_SHAPES(X)
+#undef X
+  }
+  return dispatch_generic(a, nullptr, dev, stream);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// exported C ABI
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+void mo_qp_params_default(mo_qp_params* p) {  // qp.hpp:136-163
+  if (!p) return;
+  p->initial_mu = 1.0;
+  p->sigma = 0.5;
+  p->termination_kkt_tol = 1.0e-9;
+  p->termination_complementarity_tol = 1.0e-6;
+  p->max_iterations = 10;
+  p->barrier_strategy = MO_BARRIER_COMPLEMENTARITY;
+  p->decrease_mu_only_on_small_error = 0;
+  p->initial_guess_method = MO_GUESS_NAIVE;
+  p->initialize_mu_with_complementarity = 0;
+  p->reserved = 0;
+}
+
+int64_t mo_qp_vars_stride(int32_t n, int32_t k, int32_t m) { return (int64_t)n + 2 * (int64_t)m + k; }
+
+int mo_abi_version(void) { return MO_ABI_VERSION; }
+
+int64_t mo_kernel_launch_count(void) { return g_launches.load(); }
+
+const char* mo_last_error_string(void) { return g_last_error.c_str(); }
+
+const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags) {
+  if (tpp_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY)) return "tpp";
+  switch (generic_threads(n, k)) {
+    case 32: return "generic32";
+    case 128: return "generic128";
+    default: return "generic256";
+  }
+}
+
+int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out, int device,
+                         void* cuda_stream) {
+  if (!problems || !params || !out) return MO_ERR_INVALID_ARGUMENT;
+  int rc = check_batch(problems);
+  if (rc) return rc;
+  rc = check_params(params);
+  if (rc) return rc;
+  if (problems->batch == 0) return MO_OK;
+  if (!out->vars || !out->status || !out->iters) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  const mo::QPArgs a = make_args(problems, params, out);
+  return dispatch_solve(a, dev, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int mo_qp_ip_newton_step_batch(const mo_qp_batch* problems, double mu, int32_t barrier_strategy, double* vars,
+                               double* delta_out, double* ip_out, double* kkt_out, int32_t* status, int device,
+                               void* cuda_stream) {
+  if (!problems || !vars || !status) return MO_ERR_INVALID_ARGUMENT;
+  int rc = check_batch(problems);
+  if (rc) return rc;
+  if (barrier_strategy < 0 || barrier_strategy > 2) return MO_ERR_INVALID_PARAMS;
+  if (problems->batch == 0) return MO_OK;
+  DeviceInfo dev;
+  rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  mo::QPArgs a = make_args(problems, nullptr, nullptr);
+  a.strategy = barrier_strategy;
+  a.vars = vars;
+  a.status = status;
+  mo::StepArgs sa{mu, delta_out, ip_out, kkt_out};
+  return dispatch_generic(a, &sa, dev, static_cast<cudaStream_t>(cuda_stream));
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// host-buffer entry point: chunked H2D -> solve -> D2H pipeline over three stream slots
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  char* dbuf = nullptr;
+  size_t cap = 0;
+};
+struct HostCtx {
+  Slot slots[3];
+};
+HostCtx g_host[64];
+std::mutex g_host_mu;
+
+inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+struct ChunkLayout {
+  size_t G, c, A, b, ivar, ia, ib, icount, vars, status, iters, kkt, lag, log, total;
+};
+
+ChunkLayout chunk_layout(const mo_qp_batch& B, const mo_qp_params& P, const mo_qp_out& O, long long C) {
+  ChunkLayout L{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
+  const size_t n = B.n, k = B.k, m = B.m, d = sizeof(double);
+  L.G = take(C * n * n * d);
+  L.c = take(C * n * d);
+  L.A = take(C * k * n * d);
+  L.b = take(C * k * d);
+  L.ivar = take(B.ineq_var ? C * m * sizeof(int32_t) : 0);
+  L.ia = take(B.ineq_a ? C * m * d : 0);
+  L.ib = take(C * m * d);
+  L.icount = take(B.ineq_count ? C * sizeof(int32_t) : 0);
+  L.vars = take(C * (n + 2 * m + k) * d);
+  L.status = take(C * sizeof(int32_t));
+  L.iters = take(C * sizeof(int32_t));
+  L.kkt = take(O.kkt_final ? C * 4 * d : 0);
+  L.lag = take(O.lagrange ? C * 2 * d : 0);
+  L.log = take(O.iter_log ? C * (size_t)P.max_iterations * MO_QP_ITER_LOG_STRIDE * d : 0);
+  L.total = off;
+  return L;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* mo_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    g_last_error = std::string("cudaHostAlloc: ") + cudaGetErrorString(cudaGetLastError());
+    return nullptr;
+  }
+  return p;
+}
+
+void mo_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
+                              int device) {
+  if (!problems || !params || !out) return MO_ERR_INVALID_ARGUMENT;
+  int rc = check_batch(problems);
+  if (rc) return rc;
+  rc = check_params(params);
+  if (rc) return rc;
+  const mo_qp_batch& B = *problems;
+  if (B.batch == 0) return MO_OK;
+  if (!out->vars || !out->status || !out->iters) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  std::lock_guard<std::mutex> lk(g_host_mu);
+  HostCtx& ctx = g_host[device];
+
+  const size_t n = B.n, k = B.k, m = B.m, d = sizeof(double), vs = n + 2 * m + k;
+  const size_t per_problem = (n * n + n + k * n + k + 2 * m + vs + 8) * d +
+                             (out->iter_log ? (size_t)params->max_iterations * MO_QP_ITER_LOG_STRIDE * d : 0);
+  long long C = (long long)((size_t(96) << 20) / per_problem);
+  if (C < 4096) C = 4096;
+  if (C > B.batch) C = B.batch;
+  const ChunkLayout L = chunk_layout(B, *params, *out, C);
+  for (Slot& s : ctx.slots) {
+    if (!s.stream) MO_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    if (s.cap < L.total) {
+      if (s.dbuf) MO_CUDA(cudaFree(s.dbuf));
+      s.dbuf = nullptr; s.cap = 0;
+      MO_CUDA(cudaMalloc(&s.dbuf, L.total));
+      s.cap = L.total;
+    }
+  }
+  const bool user_guess = params->initial_guess_method == MO_GUESS_USER_PROVIDED;
+  int slot_i = 0;
+  for (long long lo = 0; lo < B.batch; lo += C, slot_i = (slot_i + 1) % 3) {
+    const long long cnt = (B.batch - lo < C) ? B.batch - lo : C;
+    Slot& s = ctx.slots[slot_i];
+    MO_CUDA(cudaStreamSynchronize(s.stream));  // previous use of this slot has drained
+    char* D = s.dbuf;
+    auto h2d = [&](size_t off, const void* src, size_t stride_bytes) -> cudaError_t {
+      if (!src || !stride_bytes) return cudaSuccess;
+      return cudaMemcpyAsync(D + off, (const char*)src + lo * stride_bytes, cnt * stride_bytes,
+                             cudaMemcpyHostToDevice, s.stream);
+    };
+    MO_CUDA(h2d(L.G, B.G, n * n * d));
+    MO_CUDA(h2d(L.c, B.c, n * d));
+    MO_CUDA(h2d(L.A, B.A_eq, k * n * d));
+    MO_CUDA(h2d(L.b, B.b_eq, k * d));
+    MO_CUDA(h2d(L.ivar, B.ineq_var, m * sizeof(int32_t)));
+    MO_CUDA(h2d(L.ia, B.ineq_a, m * d));
+    MO_CUDA(h2d(L.ib, B.ineq_b, m * d));
+    MO_CUDA(h2d(L.icount, B.ineq_count, sizeof(int32_t)));
+    if (user_guess) MO_CUDA(h2d(L.vars, out->vars, vs * d));
+    mo_qp_batch db = B;
+    db.batch = cnt;
+    db.G = (const double*)(D + L.G); db.c = (const double*)(D + L.c);
+    db.A_eq = k ? (const double*)(D + L.A) : nullptr; db.b_eq = k ? (const double*)(D + L.b) : nullptr;
+    db.ineq_var = B.ineq_var ? (const int32_t*)(D + L.ivar) : nullptr;
+    db.ineq_a = B.ineq_a ? (const double*)(D + L.ia) : nullptr;
+    db.ineq_b = m ? (const double*)(D + L.ib) : nullptr;
+    db.ineq_count = B.ineq_count ? (const int32_t*)(D + L.icount) : nullptr;
+    mo_qp_out dout{};
+    dout.vars = (double*)(D + L.vars); dout.status = (int32_t*)(D + L.status); dout.iters = (int32_t*)(D + L.iters);
+    dout.kkt_final = out->kkt_final ? (double*)(D + L.kkt) : nullptr;
+    dout.lagrange = out->lagrange ? (double*)(D + L.lag) : nullptr;
+    dout.iter_log = out->iter_log ? (double*)(D + L.log) : nullptr;
+    if (dout.iter_log)
+      MO_CUDA(cudaMemsetAsync(dout.iter_log, 0xff, cnt * (size_t)params->max_iterations * MO_QP_ITER_LOG_STRIDE * d, s.stream));
+    const mo::QPArgs a = make_args(&db, params, &dout);
+    rc = dispatch_solve(a, dev, s.stream);
+    if (rc) return rc;
+    auto d2h = [&](void* dst, size_t off, size_t stride_bytes) -> cudaError_t {
+      if (!dst || !stride_bytes) return cudaSuccess;
+      return cudaMemcpyAsync((char*)dst + lo * stride_bytes, D + off, cnt * stride_bytes, cudaMemcpyDeviceToHost,
+                             s.stream);
+    };
+    MO_CUDA(d2h(out->vars, L.vars, vs * d));
+    MO_CUDA(d2h(out->status, L.status, sizeof(int32_t)));
+    MO_CUDA(d2h(out->iters, L.iters, sizeof(int32_t)));
+    MO_CUDA(d2h(out->kkt_final, L.kkt, 4 * d));
+    MO_CUDA(d2h(out->lagrange, L.lag, 2 * d));
+    MO_CUDA(d2h(out->iter_log, L.log, (size_t)params->max_iterations * MO_QP_ITER_LOG_STRIDE * d));
+  }
+  for (Slot& s : ctx.slots) MO_CUDA(cudaStreamSynchronize(s.stream));
+  return MO_OK;
+}
+
+}  // extern "C"

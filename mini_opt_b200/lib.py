@@ -1,0 +1,101 @@
+"""ctypes binding of the product library ``libminiopt_b200.so`` (CUDA kernels + C ABI, include/mini_opt_b200.h).
+
+There is no CPU fallback: every compute call goes to the CUDA path and raises if the library is missing or the
+device is not a B200-class (sm_100) GPU. Nothing under ``oracle/`` is ever imported from here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+from . import abi
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libminiopt_b200.so"
+
+EXPORTS = [
+    "mo_qp_params_default", "mo_qp_vars_stride", "mo_qp_ip_solve_batch", "mo_qp_ip_solve_batch_host",
+    "mo_qp_ip_newton_step_batch", "mo_qp_kernel_variant", "mo_kernel_launch_count", "mo_last_error_string",
+    "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak",
+]
+
+
+class MiniOptError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"mini_opt_b200 error {code}: {msg}")
+        self.code = code
+
+
+def build(verbose: bool = False) -> None:
+    """Compile the CUDA extension in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    res = subprocess.run(["make", "-C", str(PKG / "csrc"), "all"], capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout[-4000:], res.stderr[-4000:])
+    if res.returncode != 0:
+        raise RuntimeError("building libminiopt_b200.so failed")
+
+
+_lib = None
+
+
+def load():
+    """Load the product library; raises (loudly) if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise FileNotFoundError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback for the solve path)")
+    lib = C.CDLL(str(LIB_PATH))
+    BP, PP, OP = C.POINTER(abi.MoQpBatch), C.POINTER(abi.MoQpParams), C.POINTER(abi.MoQpOut)
+    lib.mo_qp_params_default.argtypes = [PP]
+    lib.mo_qp_params_default.restype = None
+    lib.mo_qp_vars_stride.argtypes = [C.c_int32] * 3
+    lib.mo_qp_vars_stride.restype = C.c_int64
+    lib.mo_qp_ip_solve_batch.argtypes = [BP, PP, OP, C.c_int, C.c_void_p]
+    lib.mo_qp_ip_solve_batch.restype = C.c_int
+    lib.mo_qp_ip_solve_batch_host.argtypes = [BP, PP, OP, C.c_int]
+    lib.mo_qp_ip_solve_batch_host.restype = C.c_int
+    lib.mo_qp_ip_newton_step_batch.argtypes = [BP, C.c_double, C.c_int32] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
+    lib.mo_qp_ip_newton_step_batch.restype = C.c_int
+    lib.mo_qp_kernel_variant.argtypes = [C.c_int32] * 4
+    lib.mo_qp_kernel_variant.restype = C.c_char_p
+    lib.mo_kernel_launch_count.restype = C.c_int64
+    lib.mo_last_error_string.restype = C.c_char_p
+    lib.mo_abi_version.restype = C.c_int
+    lib.mo_host_alloc.argtypes = [C.c_size_t]
+    lib.mo_host_alloc.restype = C.c_void_p
+    lib.mo_host_free.argtypes = [C.c_void_p]
+    lib.mo_host_free.restype = None
+    lib.mo_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    lib.mo_measure_fp64_peak.restype = C.c_int
+    if lib.mo_abi_version() != abi.MO_ABI_VERSION:
+        raise RuntimeError("libminiopt_b200.so ABI version mismatch; rebuild")
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = load().mo_last_error_string().decode() if rc in (abi.MO_ERR_CUDA, abi.MO_ERR_NO_DEVICE,
+                                                               abi.MO_ERR_UNSUPPORTED_SHAPE) else ""
+        names = {-1: "invalid argument", -2: "invalid params", -3: "unsupported shape", -4: "CUDA error",
+                 -5: "no sm_100 device"}
+        raise MiniOptError(rc, f"{names.get(rc, '?')} {msg}".strip())
+
+
+def kernel_variant(n: int, k: int, m: int, flags: int) -> str:
+    return load().mo_qp_kernel_variant(n, k, m, flags).decode()
+
+
+def launch_count() -> int:
+    return int(load().mo_kernel_launch_count())
+
+
+def measure_fp64_peak(device_index: int = 0) -> float:
+    """FP64 DFMA peak of this GPU in TFLOP/s (live microbenchmark)."""
+    v = C.c_double(0.0)
+    check(load().mo_measure_fp64_peak(int(device_index), C.byref(v)))
+    return float(v.value)
