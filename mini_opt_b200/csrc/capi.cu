@@ -130,7 +130,7 @@ int launch_tpp(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) 
   using L = mo::TppLayout<N, K>;
   constexpr int threads = 32 * kTppWarpsPerBlock;
   auto kernel = mo::qp_ip_tpp_kernel<N, K, kTppWarpsPerBlock, kTppMinBlocks>;
-  const size_t smem = sizeof(double) * L::E * (threads + 1);
+  const size_t smem = sizeof(double) * L::ETOT * (threads + 1);
   static thread_local int configured_dev = -1;
   static thread_local int blocks_per_sm = 0;
   int cur = 0;

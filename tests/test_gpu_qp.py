@@ -20,6 +20,10 @@ from mini_opt_b200 import abi, synth
 pytestmark = pytest.mark.gpu
 
 X_RTOL = 1e-9
+# Final KKT norms of a converged solve sit between the rounding floor (1e-16) and the termination tolerance
+# (1e-9) and are cancellation noise there: they are compared to rtol 1e-6 OR within the termination tolerance.
+# Norm parity where the norms carry information (1e9 .. 1e-6) is checked on the per-iteration logs.
+KKT_ATOL = 1e-9
 
 
 @pytest.fixture(scope="module")
@@ -136,8 +140,9 @@ def test_box_synth_vs_reference_golden(dev, golden_box, n, gname, guess, explici
     else:
         compare(out, R, n, min_same=0.97, min_x=0.97, min_status=0.99)
     ok = out.iters == R.iters
-    np.testing.assert_allclose(out.kkt_final[ok], g[f"{tag}_kkt"][ok], rtol=1e-3, atol=1e-12)
-    np.testing.assert_allclose(out.lagrange[ok], g[f"{tag}_lagrange"][ok], rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(out.kkt_final[ok], g[f"{tag}_kkt"][ok], rtol=1e-6, atol=KKT_ATOL)
+    tight = ok & (gu.rel_x_err(out.vars, R.vars, n) < X_RTOL)  # multipliers of the non-chaotic trajectories
+    np.testing.assert_allclose(out.lagrange[tight], g[f"{tag}_lagrange"][tight], rtol=1e-6, atol=1e-9)
     if n == 8 and gname == "naive":
         for p in range(0, arrs.batch, 17):
             its = int(out.iters[p])
@@ -156,7 +161,7 @@ def test_box_synth_vs_oracle(dev, oracle, n, k, B, guess):
         same, rel = compare(out, ref, n, min_same=0.999, min_x=0.999)
     else:
         same, rel = compare(out, ref, n, min_same=0.97, min_x=0.97, min_status=0.99)
-    np.testing.assert_allclose(out.kkt_final[same], ref.kkt_final[same], rtol=1e-2, atol=1e-11)
+    np.testing.assert_allclose(out.kkt_final[same], ref.kkt_final[same], rtol=1e-6, atol=KKT_ATOL)
 
 
 @pytest.mark.parametrize("strategy", [abi.MO_BARRIER_FIXED_DECREASE, abi.MO_BARRIER_PREDICTOR_CORRECTOR])
