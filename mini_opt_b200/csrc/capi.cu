@@ -129,22 +129,31 @@ template <int N, int K>
 int launch_tpp(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
   using L = mo::TppLayout<N, K>;
   constexpr int threads = 32 * kTppWarpsPerBlock;
-  auto kernel = mo::qp_ip_tpp_kernel<N, K, kTppWarpsPerBlock, kTppMinBlocks>;
-  const size_t smem = sizeof(double) * L::ETOT * (threads + 1);
+  auto guess = mo::qp_tpp_guess_kernel<N, K>;
+  auto iterate = mo::qp_tpp_iterate_kernel<N, K, kTppWarpsPerBlock, kTppMinBlocks>;
+  const size_t smem_guess = 0;
+  const size_t smem_iter = sizeof(double) * L::ETOT * (threads + 1);
   static thread_local int configured_dev = -1;
-  static thread_local int blocks_per_sm = 0;
+  static thread_local int bps_guess = 0, bps_iter = 0;
   int cur = 0;
   MO_CUDA(cudaGetDevice(&cur));
   if (configured_dev != cur) {
-    MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, threads, smem));
-    if (blocks_per_sm < 1) { g_last_error = "tpp kernel does not fit on an SM"; return MO_ERR_UNSUPPORTED_SHAPE; }
+    MO_CUDA(cudaFuncSetAttribute(iterate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_iter));
+    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_guess, guess, threads, smem_guess));
+    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_iter, iterate, threads, smem_iter));
+    if (bps_guess < 1 || bps_iter < 1) { g_last_error = "tpp kernels do not fit on an SM"; return MO_ERR_UNSUPPORTED_SHAPE; }
     configured_dev = cur;
   }
   const long long want = (a.batch + threads - 1) / threads;
-  const long long cap = (long long)dev.sms * blocks_per_sm;
-  const int grid = (int)(want < cap ? want : cap);
-  kernel<<<grid, threads, smem, stream>>>(a);
+  const bool user_guess = a.guess == MO_GUESS_USER_PROVIDED;
+  if (!user_guess) {  // ComputeInitialGuess -> start state in vars
+    const long long cap = (long long)dev.sms * bps_guess;
+    guess<<<(int)(want < cap ? want : cap), threads, smem_guess, stream>>>(a);
+    g_launches.fetch_add(1);
+    MO_CUDA(cudaGetLastError());
+  }
+  const long long cap = (long long)dev.sms * bps_iter;
+  iterate<<<(int)(want < cap ? want : cap), threads, smem_iter, stream>>>(a, user_guess ? 0 : 1);
   g_launches.fetch_add(1);
   MO_CUDA(cudaGetLastError());
   return MO_OK;
@@ -201,7 +210,10 @@ int dispatch_generic(const mo::QPArgs& a, const mo::StepArgs* step, const Device
 }
 
 int dispatch_solve(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
-  if (tpp_eligible(a.n, a.k, a.m, a.flags, a.icount != nullptr, a.strategy)) {
+  auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+  const bool vec_ok = aligned16(a.G) && aligned16(a.c) && aligned16(a.A) && aligned16(a.b) && aligned16(a.ib) &&
+                      aligned16(a.vars);  // the tpp kernels use 16-byte vector requests on even-length runs
+  if (vec_ok && tpp_eligible(a.n, a.k, a.m, a.flags, a.icount != nullptr, a.strategy)) {
 #define X(N_, K_) if (a.n == N_ && a.k == K_) return launch_tpp<N_, K_>(a, dev, stream);
     MO_TPP_SHAPES(X)
 #undef X

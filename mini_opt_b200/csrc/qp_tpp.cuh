@@ -7,14 +7,22 @@
 // Mapping. One THREAD owns one QP. Its reduced KKT matrix [[G+Sigma, A'],[A, 0]] lives entirely in
 // registers as a packed lower triangle and is factored by a fully unrolled LDL' without pivoting
 // (the H block is SPD, the Schur block negative definite: quasi-definite, so any order is stable);
-// the two triangular solves recover [dx; -dy]. The problem data (G lower triangle, A_eq, c, b_eq, box
-// offsets) sits in shared memory, element-major / thread-minor, so every LDS is conflict free.
-// Iteration counts differ per problem (7..30), so a warp is a pool of 32 lanes over a contiguous chunk
-// of the batch: a lane that terminates stores its result and is REFILLED with the next problem of the
-// chunk; the warp loads that problem cooperatively (coalesced 256 B requests) and transposes it into
-// the lane's shared-memory column. The equality-constrained initial guess is the same
-// assemble/factor/solve code with Sigma = 0, so refilled lanes (phase GUESS) and iterating lanes
-// (phase ITER) share the dominant part of the loop body.
+// two triangular solves recover [dx; -dy]. Problem data (G lower triangle, A_eq, c, b_eq, box offsets) and
+// the slacks / multipliers s, z sit in shared memory, element-major / thread-minor, so every LDS/STS is
+// conflict free; x and y stay in registers.
+//
+// Two kernels:
+//   qp_tpp_guess_kernel    ComputeInitialGuess for every problem, no divergence: writes the start state
+//                          [x|s|y|z] into `vars` (the buffer the result will overwrite).
+//   qp_tpp_iterate_kernel  the Newton loop from the state in `vars`. Iteration counts differ per problem
+//                          (7..30), so a warp is a pool of 32 lanes over a contiguous chunk of the batch: a lane
+//                          whose problem terminated parks its x, y in its shared-memory column, the warp
+//                          writes the 336-byte result with coalesced stores, and the lane is REFILLED with
+//                          the next problem of the chunk (problem + start state loaded cooperatively with
+//                          coalesced requests, transposed into the lane's column; the lines a warp needs
+//                          next are prefetched into L2 a few problems ahead).
+// Each round of the loop is: refill -> residuals + KKT assembly -> termination test / mu update -> LDL' +
+// solve -> step lengths + state update; the only per-lane divergence is "this lane's problem just ended".
 #pragma once
 
 #include "qp_common.cuh"
@@ -138,69 +146,162 @@ __device__ __forceinline__ double comp_err2(double sq, double sum, double mu, in
   return corrected > 0.0 ? corrected : 0.0;
 }
 
-// Store a finished problem: [x | s | y | z], status, iteration count, final KKT norms, multiplier summary.
+// Cooperative load of `cnt` (<= 32) CONSECUTIVE problems starting at q0 into the warp's columns 0..cnt-1: each
+// input array is one contiguous run, read with fully coalesced, independent 8-byte requests (unrolled so that
+// many are in flight) and scattered into the transposed layout.
 template <int N, int K>
-__device__ __forceinline__ void store_result(const QPArgs& a, long long prob, const double* __restrict__ smcol, int LD,
-                                             const double (&x)[N], const double (&y)[K > 0 ? K : 1], int status,
-                                             int iters, bool zero_state, const double (&kkt2)[4]) {
+__device__ __forceinline__ void load_block_coop(const QPArgs& a, long long q0, int cnt, double* __restrict__ wcol,
+                                                int LD, int lane) {
   using L = TppLayout<N, K>;
-  constexpr int M = L::M;
-  double* __restrict__ vp = a.vars + prob * L::STRIDE;
-#pragma unroll
-  for (int i = 0; i < N; ++i) vp[i] = zero_state ? 0.0 : x[i];
-#pragma unroll
-  for (int i = 0; i < M; ++i) {
-    vp[N + i] = zero_state ? 0.0 : smcol[(L::OS + i) * LD];
-    vp[N + M + K + i] = zero_state ? 0.0 : smcol[(L::OZ + i) * LD];
-  }
-#pragma unroll
-  for (int r = 0; r < K; ++r) vp[N + M + r] = zero_state ? 0.0 : y[r];
-  a.status[prob] = status;
-  a.iters[prob] = iters;
-  if (a.kkt_final) {
-    double* __restrict__ kf = a.kkt_final + prob * 4;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) kf[q] = sqrt(kkt2[q]);
-  }
-  if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
-    double mn = qnan(), li = qnan();
-    if (K > 0 && !zero_state) {
-      mn = y[0]; li = fabs(y[0]);
-#pragma unroll
-      for (int r = 1; r < K; ++r) { mn = y[r] < mn ? y[r] : mn; li = fabs(y[r]) > li ? fabs(y[r]) : li; }
-    } else if (K > 0) {
-      mn = 0.0; li = 0.0;
+  {
+    const double* __restrict__ src = a.G + q0 * (N * N);
+    const int total = cnt * N * N;
+#pragma unroll 8
+    for (int it = 0; it < N * N; ++it) {
+      const int idx = it * 32 + lane;
+      if (idx < total) {
+        const int pr = idx / (N * N), e = idx - pr * (N * N);
+        const int cc = e / N, rr = e - cc * N;
+        const double v = __ldg(src + idx);
+        if (rr >= cc) wcol[pr + (L::OG + lidx(rr, cc)) * LD] = v;
+      }
     }
-    a.lagrange[prob * 2] = mn;
-    a.lagrange[prob * 2 + 1] = li;
   }
+  auto run = [&](const double* __restrict__ src, int per, int slot0) {
+    const int total = cnt * per;
+#pragma unroll 8
+    for (int it = 0; it < per; ++it) {
+      const int idx = it * 32 + lane;
+      if (idx < total) {
+        const int pr = idx / per, e = idx - pr * per;
+        wcol[pr + (slot0 + e) * LD] = __ldg(src + idx);
+      }
+    }
+  };
+  if (K > 0) run(a.A + q0 * (N * K), N * K, L::OA);
+  run(a.c + q0 * N, N, L::OC);
+  if (K > 0) run(a.b + q0 * K, K, L::OB);
+  run(a.ib + q0 * L::M, L::M, L::OIB);
 }
 
-// ComputeInitialGuess tail (qp.cc:462-481): clamp x into the box in list order, s = max(1e-9, a x + b), z = 1/s.
-template <int N, int K>
-__device__ __forceinline__ void clamp_and_init_slacks(double* __restrict__ smcol, int LD, double (&x)[N]) {
-  using L = TppLayout<N, K>;
+// ComputeInitialGuess tail (qp.cc:462-481) for variable v: clamp x into the box in list order
+// (ClampX, qp.hpp:43-53), s = max(1e-9, a x + b), z = 1/s.
+__device__ __forceinline__ void clamp_and_init_pair(double& xv, double b0, double b1, double& s0, double& s1,
+                                                    double& z0, double& z1) {
+  xv = xv > -b0 ? xv : -b0;  // a = +1: max(x, -b/a)
+  xv = xv < b1 ? xv : b1;    // a = -1: min(x, b/-a)
+  s0 = fmax(1.0e-9, xv + b0);
+  s1 = fmax(1.0e-9, b1 - xv);
+  z0 = 1.0 / s0;
+  z1 = 1.0 / s1;
+}
+
+// Contiguous run of COUNT doubles owned by one thread: 16-byte vector requests when COUNT is even (the run is
+// then 16-byte aligned whenever the array base is; the host checks the bases), scalar otherwise.
+template <int COUNT>
+__device__ __forceinline__ void load_run(const double* __restrict__ p, double (&out)[COUNT > 0 ? COUNT : 1]) {
+  if (COUNT % 2 == 0) {
+    const double2* __restrict__ p2 = reinterpret_cast<const double2*>(p);
 #pragma unroll
-  for (int v = 0; v < N; ++v) {
-    const double b0 = smcol[(L::OIB + 2 * v) * LD], b1 = smcol[(L::OIB + 2 * v + 1) * LD];
-    double xv = x[v];
-    xv = xv > -b0 ? xv : -b0;  // ClampX, a = +1: max(x, -b/a)   (qp.hpp:43-53)
-    xv = xv < b1 ? xv : b1;    // ClampX, a = -1: min(x, b/-a)
-    x[v] = xv;
-    const double s0 = fmax(1.0e-9, xv + b0), s1 = fmax(1.0e-9, b1 - xv);
-    smcol[(L::OS + 2 * v) * LD] = s0;
-    smcol[(L::OS + 2 * v + 1) * LD] = s1;
-    smcol[(L::OZ + 2 * v) * LD] = 1.0 / s0;
-    smcol[(L::OZ + 2 * v + 1) * LD] = 1.0 / s1;
+    for (int i = 0; i < COUNT / 2; ++i) {
+      const double2 v = __ldg(p2 + i);
+      out[2 * i] = v.x;
+      out[2 * i + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < COUNT; ++i) out[i] = __ldg(p + i);
   }
 }
 
-template <int N, int K, int WPB, int MINB>
-__global__ void __launch_bounds__(32 * WPB, MINB) qp_ip_tpp_kernel(const QPArgs a) {
+template <int COUNT>
+__device__ __forceinline__ void store_run(double* __restrict__ p, const double (&in)[COUNT]) {
+  if (COUNT % 2 == 0) {
+    double2* __restrict__ p2 = reinterpret_cast<double2*>(p);
+#pragma unroll
+    for (int i = 0; i < COUNT / 2; ++i) p2[i] = make_double2(in[2 * i], in[2 * i + 1]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < COUNT; ++i) p[i] = in[i];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 1: ComputeInitialGuess (qp.cc:439-482) for every problem -> start state in `vars`.
+// NAIVE: x = y = 0. SOLVE_EQUALITY_CONSTRAINED: the KKT system without Sigma at x = y = 0 (r_d = c,
+// r_pe = b_eq), factored and solved in registers. A failed factorization is recorded in status[] (= 2) and
+// the iterate kernel skips the problem; otherwise status[] = -1 (in flight).
+// One thread per problem, no shared memory: each thread streams its own contiguous slices (every sector it
+// touches is fully used) with independent vector loads, so the kernel runs at memory speed.
+// ---------------------------------------------------------------------------------------------
+template <int N, int K>
+__global__ void __launch_bounds__(128) qp_tpp_guess_kernel(const QPArgs a) {
   using L = TppLayout<N, K>;
-  constexpr int P = L::P, M = L::M, LD = 32 * WPB + 1;
+  constexpr int P = L::P, M = L::M, KD = K > 0 ? K : 1, NKD = N * K > 0 ? N * K : 1;
+  const bool eq_guess = a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;
+  for (long long prob = (long long)blockIdx.x * blockDim.x + threadIdx.x; prob < a.batch;
+       prob += (long long)gridDim.x * blockDim.x) {
+    double sol[P], ib[M];
+    load_run<M>(a.ib + prob * M, ib);
+    bool ok = true;
+    if (eq_guess) {
+      double Km[L::NK], Gf[N * N], Af[NKD], cf[N], bf[KD];
+      load_run<N * N>(a.G + prob * (N * N), Gf);
+      load_run<N * K>(a.A + prob * (N * K), Af);
+      load_run<N>(a.c + prob * N, cf);
+      load_run<K>(a.b + prob * K, bf);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+#pragma unroll
+        for (int j = 0; j <= i; ++j) Km[lidx(i, j)] = Gf[j * N + i];  // column-major (i, j)
+        sol[i] = -cf[i];
+      }
+#pragma unroll
+      for (int r = 0; r < K; ++r) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) Km[lidx(N + r, j)] = Af[j * K + r];
+#pragma unroll
+        for (int q = 0; q <= r; ++q) Km[lidx(N + r, N + q)] = 0.0;
+        sol[N + r] = -bf[r];
+      }
+      ok = ldlt_solve_inreg<P>(Km, sol);  // sol = [x; -y]
+    } else {
+#pragma unroll
+      for (int i = 0; i < P; ++i) sol[i] = 0.0;
+    }
+    double out[L::STRIDE];
+#pragma unroll
+    for (int v = 0; v < N; ++v) {
+      double xv = ok ? sol[v] : 0.0, s0, s1, z0, z1;
+      clamp_and_init_pair(xv, ib[2 * v], ib[2 * v + 1], s0, s1, z0, z1);
+      out[v] = ok ? xv : 0.0;
+      out[N + 2 * v] = ok ? s0 : 0.0;
+      out[N + 2 * v + 1] = ok ? s1 : 0.0;
+      out[N + M + K + 2 * v] = ok ? z0 : 0.0;
+      out[N + M + K + 2 * v + 1] = ok ? z1 : 0.0;
+    }
+#pragma unroll
+    for (int r = 0; r < K; ++r) out[N + M + r] = ok ? -sol[N + r] : 0.0;
+    store_run<L::STRIDE>(a.vars + prob * L::STRIDE, out);
+    a.status[prob] = ok ? -1 : MO_QP_FAILED_FACTORIZATION;
+    if (!ok) {
+      a.iters[prob] = 0;
+      if (a.kkt_final) { double* kf = a.kkt_final + prob * 4; kf[0] = 0.0; kf[1] = 0.0; kf[2] = 0.0; kf[3] = 0.0; }
+      if (a.lagrange) { a.lagrange[prob * 2] = K > 0 ? 0.0 : qnan(); a.lagrange[prob * 2 + 1] = K > 0 ? 0.0 : qnan(); }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 2: the Newton loop (qp.cc:110-149) from the start state in `vars`.
+// ---------------------------------------------------------------------------------------------
+template <int N, int K, int WPB, int MINB>
+__global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QPArgs a, const int skip_failed) {
+  using L = TppLayout<N, K>;
+  constexpr int P = L::P, M = L::M, LD = 32 * WPB + 1, STRIDE = L::STRIDE;
   constexpr int KD = K > 0 ? K : 1;
   constexpr unsigned FULL = 0xffffffffu;
+  constexpr int PF_AHEAD = 8;  // problems prefetched into L2 ahead of the refill pointer
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* const smcol = smem + threadIdx.x;
@@ -211,203 +312,267 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_ip_tpp_kernel(const QPArgs 
   const long long chunk = (a.batch + nwarps - 1) / nwarps;
   long long next = gw * chunk < a.batch ? gw * chunk : a.batch;
   const long long wend = next + chunk < a.batch ? next + chunk : a.batch;
+  long long pf_next = next;
 
   const double tol2 = a.kkt_tol * a.kkt_tol;
   const double tau = 0.995;  // qp.cc:192
-  const bool eq_guess = a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;
 
   double x[N], y[KD];
   double mu = a.initial_mu, alpha_p = 1.0, alpha_d = 1.0;
   long long prob = -1;
-  int iters = 0, phase = PHASE_DEAD;
-  bool want = true, first = false;
+  int iters = 0;
+  bool live = false, fin = false, first = false;
 #pragma unroll
   for (int i = 0; i < N; ++i) x[i] = 0.0;
 #pragma unroll
   for (int i = 0; i < KD; ++i) y[i] = 0.0;
 
   for (;;) {
-    double Km[L::NK], rhs[P];
-    bool need_eval = phase == PHASE_ITER;
-    // ======== phase 1: evaluate / test termination / refill, until every live lane holds a system ========
-    for (;;) {
-      if (need_eval) {
-        need_eval = false;
-        int status = -1;
-        // ---- EvaluateKKTConditions (qp.cc:391-420) fused with the assembly of ComputeLDLT (:289-297) ----
-        double base[N];  // G_sym x + c - A'y
+    // ======== (1) write out finished problems, refill idle lanes ========
+    unsigned fmask = __ballot_sync(FULL, fin);
+    while (fmask) {  // [x|s|y|z] of lane `src`: x, y parked in slots [0, N+K) of its column, s, z in place
+      const int src = __ffs(fmask) - 1;
+      fmask &= fmask - 1;
+      const long long q = __shfl_sync(FULL, prob, src);
+      double* __restrict__ vp = a.vars + q * STRIDE;
+      const double* __restrict__ col = smwarp + src;
 #pragma unroll
-        for (int i = 0; i < N; ++i) base[i] = smcol[(L::OC + i) * LD];
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-#pragma unroll
-          for (int j = 0; j <= i; ++j) {
-            const double g = smcol[(L::OG + lidx(i, j)) * LD];
-            Km[lidx(i, j)] = g;
-            base[i] = fma(g, x[j], base[i]);
-            if (j != i) base[j] = fma(g, x[i], base[j]);
-          }
-        }
-        double npe2 = 0.0;
-#pragma unroll
-        for (int r = 0; r < K; ++r) {
-          double pe = smcol[(L::OB + r) * LD];
-#pragma unroll
-          for (int j = 0; j < N; ++j) {
-            const double av = smcol[(L::OA + j * K + r) * LD];  // A is K x N column-major
-            Km[lidx(N + r, j)] = av;
-            base[j] = fma(-av, y[r], base[j]);
-            pe = fma(av, x[j], pe);
-          }
-#pragma unroll
-          for (int q = 0; q <= r; ++q) Km[lidx(N + r, N + q)] = 0.0;
-          rhs[N + r] = -pe;
-          npe2 = fma(pe, pe, npe2);
-        }
-        double qv[N], tv[N];
-        double nd2 = 0.0, npi2 = 0.0, sq = 0.0, sum = 0.0;
-        bool spos = true;
-#pragma unroll
-        for (int v = 0; v < N; ++v) {
-          const double s0 = smcol[(L::OS + 2 * v) * LD], s1 = smcol[(L::OS + 2 * v + 1) * LD];
-          const double z0 = smcol[(L::OZ + 2 * v) * LD], z1 = smcol[(L::OZ + 2 * v + 1) * LD];
-          spos = spos && (s0 > 0.0) && (s1 > 0.0);  // F_ASSERT(all s > 0), qp.cc:285
-          const double p0 = (x[v] + smcol[(L::OIB + 2 * v) * LD]) - s0;      // r_pi, a = +1
-          const double p1 = (smcol[(L::OIB + 2 * v + 1) * LD] - x[v]) - s1;  // r_pi, a = -1
-          const double i0 = fast_rcp(s0), i1 = fast_rcp(s1);
-          const double w0 = z0 * i0, w1 = z1 * i1;  // Sigma = z / s
-          Km[lidx(v, v)] = (Km[lidx(v, v)] + w0) + w1;
-          const double rdv = (base[v] - z0) + z1;  // r_d
-          nd2 = fma(rdv, rdv, nd2);
-          npi2 = fma(p0, p0, npi2);
-          npi2 = fma(p1, p1, npi2);
-          const double c0 = s0 * z0, c1 = s1 * z1;  // r_comp
-          sq = fma(c0, c0, sq);
-          sq = fma(c1, c1, sq);
-          sum += c0;
-          sum += c1;
-          // r_aug = r_d + sum a [w r_pi + (s z - mu)/s]  (qp.cc:337-342)  ==  base + (w0 p0 - w1 p1) - mu (1/s0 - 1/s1)
-          qv[v] = fma(w0, p0, -(w1 * p1));
-          tv[v] = i0 - i1;
-        }
-        // ---- Solve loop bookkeeping (qp.cc:110-146): errors of the step just taken, termination, mu ----
-        const double mu_c = sum / (double)M;  // ComputeMu, qp.cc:509-516
-        double kkt2[4] = {nd2, 0.0, npe2, npi2};
-        if (first) {
-          first = false;
-          mu = a.init_mu_with_comp ? mu_c : a.initial_mu;  // qp.cc:115
-        } else {
-          kkt2[1] = comp_err2(sq, sum, mu, M);  // kkt_final of the iteration uses the mu it was taken with
-          const double max2 = fmax(fmax(kkt2[0], kkt2[1]), fmax(kkt2[2], kkt2[3]));
-          if (a.iter_log) {
-            double* __restrict__ row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
-            row[4] = sqrt(kkt2[0]); row[5] = sqrt(kkt2[1]); row[6] = sqrt(kkt2[2]); row[7] = sqrt(kkt2[3]);
-            row[8] = mu; row[9] = alpha_p; row[10] = alpha_d;
-            row[11] = qnan(); row[12] = qnan(); row[13] = qnan();
-          }
-          ++iters;
-          if (max2 < tol2 && mu_c < a.comp_tol) {  // qp.cc:132-137
-            status = MO_QP_SATISFIED_KKT_TOL;
-          } else if (iters >= a.max_iterations) {
-            status = MO_QP_MAX_ITERATIONS;
-          } else if (max2 <= mu * mu || !a.decrease_mu_only_on_small_error) {  // qp.cc:140-146
-            mu = (a.strategy == MO_BARRIER_FIXED_DECREASE) ? mu * a.sigma : a.sigma * mu_c;
-          }
-        }
-        if (status < 0 && !spos) {
-          status = MO_QP_NONPOSITIVE_SLACK;
-          kkt2[0] = 0.0; kkt2[1] = 0.0; kkt2[2] = 0.0; kkt2[3] = 0.0;
-        }
-        if (status >= 0) {
-          store_result<N, K>(a, prob, smcol, LD, x, y, status, iters, false, kkt2);
-          want = true;
-          phase = PHASE_DEAD;
-        } else {
-          if (a.iter_log) {  // kkt_initial of the coming iteration: ComputeErrors with the updated mu (qp.cc:118)
-            double* __restrict__ row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
-            row[0] = sqrt(nd2); row[1] = sqrt(comp_err2(sq, sum, mu, M)); row[2] = sqrt(npe2); row[3] = sqrt(npi2);
-          }
-#pragma unroll
-          for (int v = 0; v < N; ++v) rhs[v] = -fma(-mu, tv[v], base[v] + qv[v]);
+      for (int e0 = 0; e0 < STRIDE; e0 += 32) {
+        const int e = e0 + lane;
+        if (e < STRIDE) {
+          const int slot = e < N ? e : (e < N + M ? L::OS + (e - N) : (e < N + M + K ? N + (e - N - M) : L::OZ + (e - N - M - K)));
+          vp[e] = col[slot * LD];
         }
       }
-
-      // ---- refill lanes whose problem finished (or that never had one) ----
-      const unsigned need = __ballot_sync(FULL, want);
-      if (need == 0u) break;
-      const int rank = __popc(need & ((1u << lane) - 1u));
-      if (want) prob = (next + rank < wend) ? next + rank : -1;
-      next += __popc(need);
-      unsigned todo = need;
+    }
+    fin = false;
+    const unsigned idle = __ballot_sync(FULL, !live);
+    if (idle != 0u && next < wend) {
+      const int rank = __popc(idle & ((1u << lane) - 1u));
+      const bool take = !live && (next + rank < wend);
+      if (take) prob = next + rank;
+      const unsigned tmask = __ballot_sync(FULL, take);
+      next += __popc(idle);
+      if (next > wend) next = wend;
+      // the lane's own x, y and the guess kernel's verdict first: their latency overlaps the cooperative loads
+      double xin[N], yin[KD];
+      int st_in = -1;
+      if (take) {
+        const double* __restrict__ vp = a.vars + prob * STRIDE;
+#pragma unroll
+        for (int i = 0; i < N; ++i) xin[i] = __ldg(vp + i);
+#pragma unroll
+        for (int r = 0; r < K; ++r) yin[r] = __ldg(vp + N + M + r);
+        if (skip_failed) st_in = a.status[prob];
+      }
+      // cooperative loads, up to 4 problems per pass: every load of a pass is issued before its first store
+      constexpr int GL = (N * N + 31) / 32, REST = N * K + N + K + M, RL = (REST + 31) / 32;
+      unsigned todo = tmask;
       while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const long long q = __shfl_sync(FULL, prob, src);
-        if (q >= 0) load_problem_coop<N, K>(a, q, smwarp + src, LD, lane);
-      }
-      __syncwarp();
-      if (want) {
-        want = false;
-        iters = 0;
-        alpha_p = 1.0; alpha_d = 1.0;
-        if (prob < 0) {
-          phase = PHASE_DEAD;
-        } else if (eq_guess) {
-          // equality-constrained guess (qp.cc:452-460): the KKT system without Sigma at x = y = 0,
-          // where r_d = c and r_pe = b_eq
-          phase = PHASE_GUESS;
+        int src[4];
+        long long q[4];
+        bool valid[4];
 #pragma unroll
-          for (int i = 0; i < L::NG; ++i) Km[i] = smcol[(L::OG + i) * LD];
+        for (int g = 0; g < 4; ++g) {
+          valid[g] = todo != 0u;
+          src[g] = valid[g] ? __ffs(todo) - 1 : 0;
+          todo &= todo - 1;  // 0 stays 0
+          q[g] = __shfl_sync(FULL, prob, src[g]);
+        }
+        double gv[4][GL], rv[4][RL], sz[4][2];
 #pragma unroll
-          for (int r = 0; r < K; ++r) {
+        for (int g = 0; g < 4; ++g) {
+          if (valid[g]) {
+            const double* __restrict__ Gp = a.G + q[g] * (N * N);
 #pragma unroll
-            for (int j = 0; j < N; ++j) Km[lidx(N + r, j)] = smcol[(L::OA + j * K + r) * LD];
-#pragma unroll
-            for (int q = 0; q <= r; ++q) Km[lidx(N + r, N + q)] = 0.0;
-            rhs[N + r] = -smcol[(L::OB + r) * LD];
-          }
-#pragma unroll
-          for (int i = 0; i < N; ++i) rhs[i] = -smcol[(L::OC + i) * LD];
-        } else {
-          phase = PHASE_ITER;
-          first = true;
-          need_eval = true;
-          if (a.guess == MO_GUESS_USER_PROVIDED) {
-            const double* __restrict__ vp = a.vars + prob * L::STRIDE;
-#pragma unroll
-            for (int i = 0; i < N; ++i) x[i] = vp[i];
-#pragma unroll
-            for (int i = 0; i < M; ++i) {
-              smcol[(L::OS + i) * LD] = vp[N + i];
-              smcol[(L::OZ + i) * LD] = vp[N + M + K + i];
+            for (int u = 0; u < GL; ++u) {
+              const int e = u * 32 + lane;
+              gv[g][u] = (e < N * N) ? __ldg(Gp + e) : 0.0;
             }
 #pragma unroll
-            for (int r = 0; r < K; ++r) y[r] = vp[N + M + r];
-          } else {  // NAIVE: x = y = 0
+            for (int u = 0; u < RL; ++u) {
+              const int e = u * 32 + lane;
+              double v = 0.0;
+              if (e < REST) {
+                if (K > 0 && e < N * K) v = __ldg(a.A + q[g] * (N * K) + e);
+                else if (e < N * K + N) v = __ldg(a.c + q[g] * N + (e - N * K));
+                else if (K > 0 && e < N * K + N + K) v = __ldg(a.b + q[g] * K + (e - N * K - N));
+                else v = __ldg(a.ib + q[g] * M + (e - N * K - N - K));
+              }
+              rv[g][u] = v;
+            }
+            const double* __restrict__ vp = a.vars + q[g] * STRIDE;  // start state s, z
+            sz[g][0] = (lane < M) ? __ldg(vp + N + lane) : 0.0;
+            sz[g][1] = (lane < M) ? __ldg(vp + N + M + K + lane) : 0.0;
+          }
+        }
 #pragma unroll
-            for (int i = 0; i < N; ++i) x[i] = 0.0;
+        for (int g = 0; g < 4; ++g) {
+          if (valid[g]) {
+            double* __restrict__ col = smwarp + src[g];
 #pragma unroll
-            for (int r = 0; r < K; ++r) y[r] = 0.0;
-            clamp_and_init_slacks<N, K>(smcol, LD, x);
+            for (int u = 0; u < GL; ++u) {
+              const int e = u * 32 + lane;
+              const int cc = e / N, rr = e - cc * N;  // column-major (rr, cc)
+              if (e < N * N && rr >= cc) col[(L::OG + lidx(rr, cc)) * LD] = gv[g][u];
+            }
+#pragma unroll
+            for (int u = 0; u < RL; ++u) {
+              const int e = u * 32 + lane;
+              if (e < REST) col[(L::OA + e) * LD] = rv[g][u];  // OA, OC, OB, OIB are consecutive
+            }
+            if (lane < M) {
+              col[(L::OS + lane) * LD] = sz[g][0];
+              col[(L::OZ + lane) * LD] = sz[g][1];
+            }
           }
         }
       }
-      if (!__any_sync(FULL, need_eval)) break;
+      if (take) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) x[i] = xin[i];
+#pragma unroll
+        for (int r = 0; r < K; ++r) y[r] = yin[r];
+        live = st_in != MO_QP_FAILED_FACTORIZATION;
+        first = true;
+        iters = 0;
+        alpha_p = 1.0; alpha_d = 1.0;
+      }
+      // L2 prefetch of the lines the next refills will touch
+      const long long pf_end = next + PF_AHEAD < wend ? next + PF_AHEAD : wend;
+      if (pf_next < next) pf_next = next;
+      for (; pf_next < pf_end; ++pf_next) {
+        const char* p = nullptr;
+        if (lane < 4) p = (const char*)(a.G + pf_next * (N * N)) + lane * 128;
+        else if (lane == 4) p = (const char*)(a.ib + pf_next * M);
+        else if (lane == 5) p = (const char*)(a.c + pf_next * N);
+        else if (lane == 6 && K > 0) p = (const char*)(a.A + pf_next * (N * K));
+        else if (lane == 7 && K > 0) p = (const char*)(a.b + pf_next * K);
+        else if (lane >= 8 && lane < 11) p = (const char*)(a.vars + pf_next * STRIDE) + (lane - 8) * 128;
+        if (p != nullptr && (lane >= 4 || lane * 128 < N * N * 8) && (lane < 8 || (lane - 8) * 128 < STRIDE * 8))
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+      }
+      __syncwarp();
     }
-    if (__all_sync(FULL, phase == PHASE_DEAD)) break;
+    if (!__any_sync(FULL, live)) {
+      if (next >= wend) break;
+      continue;
+    }
+    int done_status = -1;
+    double rhs[P], hd[N];  // right-hand side, diagonal of G + Sigma
 
-    // ======== phase 2: factor the reduced KKT system and solve: rhs <- [dx; -dy] ========
+    if (live) {
+      // ======== (2) EvaluateKKTConditions (qp.cc:391-420) fused with the assembly of ComputeLDLT (:289-297) ========
+      double base[N];  // G_sym x + c - A'y
+#pragma unroll
+      for (int i = 0; i < N; ++i) base[i] = smcol[(L::OC + i) * LD];
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+#pragma unroll
+        for (int j = 0; j <= i; ++j) {
+          const double g = smcol[(L::OG + lidx(i, j)) * LD];
+          if (j == i) hd[i] = g;
+          base[i] = fma(g, x[j], base[i]);
+          if (j != i) base[j] = fma(g, x[i], base[j]);
+        }
+      }
+      double npe2 = 0.0;
+#pragma unroll
+      for (int r = 0; r < K; ++r) {
+        double pe = smcol[(L::OB + r) * LD];
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const double av = smcol[(L::OA + j * K + r) * LD];  // A is K x N column-major
+          base[j] = fma(-av, y[r], base[j]);
+          pe = fma(av, x[j], pe);
+        }
+        rhs[N + r] = -pe;
+        npe2 = fma(pe, pe, npe2);
+      }
+      double tv[N];
+      double nd2 = 0.0, npi2 = 0.0, sq = 0.0, sum = 0.0;
+      bool spos = true;
+#pragma unroll
+      for (int v = 0; v < N; ++v) {
+        const double s0 = smcol[(L::OS + 2 * v) * LD], s1 = smcol[(L::OS + 2 * v + 1) * LD];
+        const double z0 = smcol[(L::OZ + 2 * v) * LD], z1 = smcol[(L::OZ + 2 * v + 1) * LD];
+        spos = spos && (s0 > 0.0) && (s1 > 0.0);  // F_ASSERT(all s > 0), qp.cc:285
+        const double p0 = (x[v] + smcol[(L::OIB + 2 * v) * LD]) - s0;      // r_pi, a = +1
+        const double p1 = (smcol[(L::OIB + 2 * v + 1) * LD] - x[v]) - s1;  // r_pi, a = -1
+        const double i0 = fast_rcp(s0), i1 = fast_rcp(s1);
+        const double w0 = z0 * i0, w1 = z1 * i1;  // Sigma = z / s
+        hd[v] = (hd[v] + w0) + w1;
+        const double rdv = (base[v] - z0) + z1;  // r_d
+        nd2 = fma(rdv, rdv, nd2);
+        npi2 = fma(p0, p0, npi2);
+        npi2 = fma(p1, p1, npi2);
+        const double c0 = s0 * z0, c1 = s1 * z1;  // r_comp
+        sq = fma(c0, c0, sq);
+        sq = fma(c1, c1, sq);
+        sum += c0;
+        sum += c1;
+        // r_aug = r_d + sum a [w r_pi + (s z - mu)/s]  (qp.cc:337-342)  ==  base + (w0 p0 - w1 p1) - mu (1/s0 - 1/s1)
+        base[v] += fma(w0, p0, -(w1 * p1));
+        tv[v] = i0 - i1;
+      }
+      // ---- Solve loop bookkeeping (qp.cc:110-146): errors of the step just taken, termination, mu ----
+      const double mu_c = sum / (double)M;  // ComputeMu, qp.cc:509-516
+      if (first) {
+        first = false;
+        mu = a.init_mu_with_comp ? mu_c : a.initial_mu;  // qp.cc:115
+      } else {
+        const double comp2 = comp_err2(sq, sum, mu, M);  // kkt_final uses the mu the step was taken with
+        const double max2 = fmax(fmax(nd2, comp2), fmax(npe2, npi2));
+        if (a.iter_log) {
+          double* __restrict__ row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+          row[4] = sqrt(nd2); row[5] = sqrt(comp2); row[6] = sqrt(npe2); row[7] = sqrt(npi2);
+          row[8] = mu; row[9] = alpha_p; row[10] = alpha_d;
+          row[11] = qnan(); row[12] = qnan(); row[13] = qnan();
+        }
+        ++iters;
+        if (max2 < tol2 && mu_c < a.comp_tol) {  // qp.cc:132-137
+          done_status = MO_QP_SATISFIED_KKT_TOL;
+        } else if (iters >= a.max_iterations) {
+          done_status = MO_QP_MAX_ITERATIONS;
+        } else if (max2 <= mu * mu || !a.decrease_mu_only_on_small_error) {  // qp.cc:140-146
+          mu = (a.strategy == MO_BARRIER_FIXED_DECREASE) ? mu * a.sigma : a.sigma * mu_c;
+        }
+        if (done_status >= 0 && a.kkt_final) {
+          double* __restrict__ kf = a.kkt_final + prob * 4;
+          kf[0] = sqrt(nd2); kf[1] = sqrt(comp2); kf[2] = sqrt(npe2); kf[3] = sqrt(npi2);
+        }
+      }
+      if (done_status < 0 && !spos) done_status = MO_QP_NONPOSITIVE_SLACK;
+      if (done_status < 0 && a.iter_log) {  // kkt_initial of the coming iteration (ComputeErrors with the new mu, qp.cc:118)
+        double* __restrict__ row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+        row[0] = sqrt(nd2); row[1] = sqrt(comp_err2(sq, sum, mu, M)); row[2] = sqrt(npe2); row[3] = sqrt(npi2);
+      }
+#pragma unroll
+      for (int v = 0; v < N; ++v) rhs[v] = -fma(-mu, tv[v], base[v]);
+    }
+
+    // ======== (3) reduced KKT matrix [[G + Sigma, .],[A, 0]] (qp.cc:289-297) into registers, LDL', solve:
+    //              rhs <- [dx; -dy]. Only the diagonal differs from the copy in shared memory. ========
+    double Km[L::NK];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+#pragma unroll
+      for (int j = 0; j < i; ++j) Km[lidx(i, j)] = smcol[(L::OG + lidx(i, j)) * LD];
+      Km[lidx(i, i)] = hd[i];
+    }
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+#pragma unroll
+      for (int j = 0; j < N; ++j) Km[lidx(N + r, j)] = smcol[(L::OA + j * K + r) * LD];
+#pragma unroll
+      for (int q = 0; q <= r; ++q) Km[lidx(N + r, N + q)] = 0.0;
+    }
     const bool ok = ldlt_solve_inreg<P>(Km, rhs);
+    if (live && done_status < 0 && !ok) done_status = MO_QP_FAILED_FACTORIZATION;  // qp.cc:303-307, per problem
 
-    if (phase != PHASE_DEAD && !ok) {
-      // FailedFactorization (qp.cc:303-307) as a per-problem status; the state is left as it was
-      const double zero4[4] = {0.0, 0.0, 0.0, 0.0};
-      store_result<N, K>(a, prob, smcol, LD, x, y, MO_QP_FAILED_FACTORIZATION, iters, phase == PHASE_GUESS, zero4);
-      want = true;
-      phase = PHASE_DEAD;
-    } else if (phase == PHASE_ITER) {
-      // ======== phase 3: ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199) ========
-      double sv[M], zv[M], ds[M], dz[M];
+    if (live && done_status < 0) {
+      // ======== (4) ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199) ========
+      double ds[M], dz[M];
       double bvp = 1.0, bdp = -1.0, bvd = 1.0, bdd = -1.0;
       bool anyp = false, anyd = false;
 #pragma unroll
@@ -421,7 +586,6 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_ip_tpp_kernel(const QPArgs 
         // dz = -(z/s) ds - (s z - mu)/s  =  mu/s - (z/s) ds - z
         const double e0 = fma(mu, i0, -fma(z0 * i0, d0, z0));
         const double e1 = fma(mu, i1, -fma(z1 * i1, d1, z1));
-        sv[2 * v] = s0; sv[2 * v + 1] = s1; zv[2 * v] = z0; zv[2 * v + 1] = z1;
         ds[2 * v] = d0; ds[2 * v + 1] = d1; dz[2 * v] = e0; dz[2 * v + 1] = e1;
         alpha_accumulate(s0, d0, bvp, bdp, anyp);
         alpha_accumulate(s1, d1, bvp, bdp, anyp);
@@ -436,19 +600,37 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_ip_tpp_kernel(const QPArgs 
       for (int r = 0; r < K; ++r) y[r] = fma(-rhs[N + r], alpha_d, y[r]);
 #pragma unroll
       for (int i = 0; i < M; ++i) {
-        smcol[(L::OS + i) * LD] = fma(ds[i], alpha_p, sv[i]);
-        smcol[(L::OZ + i) * LD] = fma(dz[i], alpha_d, zv[i]);
+        smcol[(L::OS + i) * LD] = fma(ds[i], alpha_p, smcol[(L::OS + i) * LD]);
+        smcol[(L::OZ + i) * LD] = fma(dz[i], alpha_d, smcol[(L::OZ + i) * LD]);
       }
-    } else if (phase == PHASE_GUESS) {
-      // x, y of the equality-constrained problem, then clamp / slack initialisation (qp.cc:455-481)
-#pragma unroll
-      for (int i = 0; i < N; ++i) x[i] = rhs[i];
-#pragma unroll
-      for (int r = 0; r < K; ++r) y[r] = -rhs[N + r];
-      clamp_and_init_slacks<N, K>(smcol, LD, x);
-      phase = PHASE_ITER;
-      first = true;
     }
+
+    if (live && done_status >= 0) {
+      // ======== (5) this lane's problem ended: park x, y for the warp's coalesced store, scalar outputs ========
+#pragma unroll
+      for (int i = 0; i < N; ++i) smcol[i * LD] = x[i];
+#pragma unroll
+      for (int r = 0; r < K; ++r) smcol[(N + r) * LD] = y[r];
+      a.status[prob] = done_status;
+      a.iters[prob] = iters;
+      if (done_status >= MO_QP_FAILED_FACTORIZATION && a.kkt_final) {
+        double* __restrict__ kf = a.kkt_final + prob * 4;
+        kf[0] = 0.0; kf[1] = 0.0; kf[2] = 0.0; kf[3] = 0.0;
+      }
+      if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
+        double mn = qnan(), li = qnan();
+        if (K > 0) {
+          mn = y[0]; li = fabs(y[0]);
+#pragma unroll
+          for (int r = 1; r < K; ++r) { mn = y[r] < mn ? y[r] : mn; li = fabs(y[r]) > li ? fabs(y[r]) : li; }
+        }
+        a.lagrange[prob * 2] = mn;
+        a.lagrange[prob * 2 + 1] = li;
+      }
+      fin = true;
+      live = false;
+    }
+    __syncwarp();
   }
 }
 
