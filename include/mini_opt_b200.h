@@ -151,6 +151,152 @@ int mo_qp_ip_newton_step_batch(const mo_qp_batch* problems, double mu, int32_t b
                                double* vars, double* delta_out, double* ip_out, double* kkt_out,
                                int32_t* status, int device, void* cuda_stream);
 
+/* =====================================================================================================
+ * Nonlinear least squares: Gauss-Newton / Levenberg-Marquardt linearization and the SQP loop
+ * (ConstrainedNonlinearLeastSquares, include/mini_opt/nonlinear.hpp, source/nonlinear.cc)
+ * ===================================================================================================== */
+
+/* LineSearchStrategy, include/mini_opt/structs.hpp:146-151 */
+enum { MO_LS_ARMIJO_BACKTRACK = 0, MO_LS_POLYNOMIAL_APPROXIMATION = 1 };
+/* NLSTerminationState, include/mini_opt/structs.hpp:233-248 */
+enum {
+  MO_NLS_MAX_ITERATIONS = 0,
+  MO_NLS_SATISFIED_ABSOLUTE_TOL = 1,
+  MO_NLS_SATISFIED_RELATIVE_TOL = 2,
+  MO_NLS_SATISFIED_FIRST_ORDER_TOL = 3,
+  MO_NLS_MAX_LAMBDA = 4,
+  MO_NLS_QP_INDEFINITE = 5,
+  MO_NLS_USER_CALLBACK = 6,
+  /* batched stand-ins for exceptions: the inner QP threw FailedFactorization / hit F_ASSERT(s > 0) */
+  MO_NLS_QP_FAILED = 7
+};
+/* Retraction (nonlinear.hpp:127). 0: x + alpha dx (nonlinear.cc:166).  1: ModPi(x + alpha dx)
+ * (geometry_utils/angle_utils.hpp:9-17), the retraction every actuator-chain test installs
+ * (test/nonlinear_test.cc:864-870, 1076-1082). */
+enum { MO_RETRACT_ADD = 0, MO_RETRACT_MOD_PI = 1 };
+
+/* ConstrainedNonlinearLeastSquares::Params, include/mini_opt/nonlinear.hpp:37-124 (same defaults via
+ * mo_nls_params_default). log_qp_eigenvalues has no batched equivalent. */
+typedef struct mo_nls_params {
+  int32_t max_iterations;
+  int32_t max_qp_iterations;
+  double termination_kkt_tolerance;
+  double absolute_exit_tol;
+  double relative_exit_tol;
+  double absolute_first_derivative_tol;
+  int32_t max_line_search_iterations;
+  int32_t line_search_strategy;
+  double armijo_search_tau;
+  double equality_penalty_initial;
+  double equality_penalty_scale_factor;
+  double equality_penalty_rho;
+  double lambda_initial;
+  double lambda_failure_init;
+  double lambda_decrease_on_success;
+  double lambda_decrease_on_restore;
+  double max_lambda;
+  double min_lambda;
+  int32_t retraction; /* MO_RETRACT_* */
+  int32_t reserved;
+} mo_nls_params;
+
+void mo_nls_params_default(mo_nls_params* p);
+
+/*
+ * Replaces: ConstrainedNonlinearLeastSquares::LinearizeAndFillQP (source/nonlinear.cc:170-214) with
+ * Residual::Model::UpdateHessian / UpdateJacobian (include/mini_opt/residual.hpp:186-250) for problems whose
+ * residuals are supplied as dense per-problem Jacobians evaluated at x:
+ *   G  = sum over cost residual blocks of J_b' J_b  (lower triangle; strict upper triangle exactly 0)  + lambda I
+ *   c  = sum J_b' r_b,   f = sum 1/2 |r_b|^2,   A_eq = J_eq, b_eq = r_eq, equality = |r_eq|_1,
+ *   constraint i shifted to the linearization point: (v, a, a x_v + b)   (qp.hpp:57-59)
+ * All pointers are DEVICE pointers; asynchronous on cuda_stream.
+ */
+typedef struct mo_nls_linearize_args {
+  int32_t n;          /* variables                                                      */
+  int32_t r_cost;     /* total cost rows                                                */
+  int32_t cost_block; /* rows per cost Residual (r_cost % cost_block == 0; 0 -> one block) */
+  int32_t r_eq;       /* equality rows (k of the QP)                                    */
+  int32_t m;          /* inequality constraints                                         */
+  int32_t reserved;
+  int64_t batch;
+  const double* x;        /* [batch][n]                                  */
+  const double* J_cost;   /* [batch][r_cost*n] column-major r_cost x n   */
+  const double* r_cost_v; /* [batch][r_cost]                             */
+  const double* J_eq;     /* [batch][r_eq*n] column-major (NULL if r_eq == 0) */
+  const double* r_eq_v;   /* [batch][r_eq]                               */
+  const double* lambda;   /* [batch] LM damping per problem              */
+  const int32_t* ineq_var;/* [batch][m]                                  */
+  const double* ineq_a;   /* [batch][m]                                  */
+  const double* ineq_b;   /* [batch][m]                                  */
+  /* outputs: exactly the arrays of a mo_qp_batch with (n, k = r_eq, m) */
+  double* G;              /* [batch][n*n]                                */
+  double* c;              /* [batch][n]                                  */
+  double* A_eq;           /* [batch][r_eq*n]                             */
+  double* b_eq;           /* [batch][r_eq]                               */
+  double* ineq_b_shifted; /* [batch][m]                                  */
+  double* errors;         /* [batch][2] Errors{f, equality} (structs.hpp:169-186) */
+} mo_nls_linearize_args;
+
+int mo_nls_linearize_batch(const mo_nls_linearize_args* args, int device, void* cuda_stream);
+
+/*
+ * The transform-chain residual family (test/transform_chains.hpp:118-211): every problem of the batch is one
+ * ActuatorChain of `links` links with the same activity masks. Link i is Pose(q_i, t_i) (parent_T_child); the
+ * active Euler angles (XYZ composition, so3.hpp:293-338) and translations of all links, in link order, are the
+ * n optimisation variables. Residual rows are linear functionals of the effector translation:
+ *     row = w . root_t_effector - target
+ * (the y_res / x_eq residuals of test/nonlinear_test.cc:840-859). Inequalities are (var, a, b) triplets shared
+ * by the whole batch (joint limits).
+ */
+typedef struct mo_chain_ik_batch {
+  int32_t links;
+  int32_t n;          /* = number of non-zero mask entries                                   */
+  int32_t n_cost;     /* cost rows                                                            */
+  int32_t cost_block; /* rows per cost Residual (0 -> one block)                              */
+  int32_t n_eq;       /* equality rows                                                        */
+  int32_t m;          /* inequality constraints                                               */
+  int64_t batch;
+  const double* link_pose;   /* [links][7] = (qw, qx, qy, qz, tx, ty, tz), shared by the batch  */
+  const uint8_t* link_mask;  /* [links][6] = active {rx, ry, rz, tx, ty, tz}                     */
+  const double* cost_w;      /* [n_cost][3], shared                                              */
+  const double* cost_target; /* [batch][n_cost]                                                  */
+  const double* eq_w;        /* [n_eq][3], shared (NULL if n_eq == 0)                            */
+  const double* eq_target;   /* [batch][n_eq]                                                    */
+  const int32_t* ineq_var;   /* [m] shared                                                       */
+  const double* ineq_a;      /* [m]                                                              */
+  const double* ineq_b;      /* [m]                                                              */
+  const double* x0;          /* [batch][n] initial variables                                     */
+} mo_chain_ik_batch;
+
+typedef struct mo_nls_out {
+  double* x;              /* [batch][n] nls.variables() after Solve                                  */
+  int32_t* termination;   /* [batch] MO_NLS_*                                                        */
+  int32_t* iterations;    /* [batch] outputs.iterations.size()                                       */
+  int32_t* qp_iterations; /* [batch] total interior point iterations (Newton steps) over all QPs     */
+  int32_t* ls_steps;      /* [batch] total line search evaluations (NUM_LINE_SEARCH_STEPS)           */
+  double* errors;         /* optional [batch][2]: Errors{f, equality} at the returned x              */
+} mo_nls_out;
+
+/*
+ * Replaces: ActuatorChain::Update (test/transform_chains.cc:165-244) for `batch` parameter vectors.
+ *   params [batch][n];  translation [batch][3];  rotation_q [batch][4] (w,x,y,z);  t_D_params, r_D_params
+ *   [batch][3*n] column-major 3 x n. Any output may be NULL. The chain description comes from `chain`
+ *   (links, n, batch, link_pose, link_mask; the other fields are ignored).
+ */
+int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, double* translation,
+                      double* rotation_q, double* t_D_params, double* r_D_params, int device, void* cuda_stream);
+
+/*
+ * Replaces: ConstrainedNonlinearLeastSquares::Solve (source/nonlinear.cc:75-158) -- LinearizeAndFillQP,
+ * ComputeStepDirection (interior point QP, :216-259), ComputeQPCostDerivative, SelectPenalty, SelectStepSize,
+ * UpdateLambdaAndCheckExitConditions -- for every problem of a transform-chain batch, entirely on the device.
+ * Problems with equality constraints and NO inequalities would use QPNullSpaceSolver in the reference
+ * (nonlinear.cc:83-89); that solver is out of scope and such batches return
+ * MO_ERR_UNSUPPORTED_SHAPE. Device pointers, asynchronous on cuda_stream.
+ */
+int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_params* params,
+                                const mo_nls_out* out, int device, void* cuda_stream);
+
 /* Name of the kernel variant mo_qp_ip_solve_batch would launch for this shape ("warp16", "cta", ...). */
 const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags);
 

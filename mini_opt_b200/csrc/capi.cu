@@ -452,3 +452,164 @@ int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* p
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// nonlinear least squares entry points
+// ---------------------------------------------------------------------------------------------
+#include "nls_chain.cuh"
+
+namespace {
+
+// CheckParams, nonlinear.cc:49-73
+int check_nls_params(const mo_nls_params* p) {
+  const bool ok =
+      p->max_iterations >= 0 && p->max_qp_iterations >= 1 && p->termination_kkt_tolerance > 0 &&
+      p->absolute_exit_tol > 0 && p->max_line_search_iterations >= 0 && p->relative_exit_tol >= 0 &&
+      p->relative_exit_tol <= 1 && p->absolute_first_derivative_tol >= 0 && p->armijo_search_tau > 0 &&
+      p->armijo_search_tau < 1 && p->equality_penalty_initial >= 0 && p->equality_penalty_scale_factor >= 1.0 &&
+      p->equality_penalty_rho >= 0 && p->equality_penalty_rho < 1 && p->max_lambda >= 0 &&
+      p->min_lambda <= p->max_lambda && p->lambda_initial >= p->min_lambda && p->lambda_initial <= p->max_lambda &&
+      p->lambda_failure_init >= 0 && p->lambda_decrease_on_success >= 0 && p->lambda_decrease_on_success < 1.0 &&
+      p->lambda_decrease_on_restore >= 0 && p->lambda_decrease_on_restore < 1.0 &&
+      (p->line_search_strategy == MO_LS_ARMIJO_BACKTRACK || p->line_search_strategy == MO_LS_POLYNOMIAL_APPROXIMATION) &&
+      (p->retraction == MO_RETRACT_ADD || p->retraction == MO_RETRACT_MOD_PI) && p->max_line_search_iterations < 40;
+  return ok ? MO_OK : MO_ERR_INVALID_PARAMS;
+}
+
+int check_chain(const mo_chain_ik_batch* b, bool fk_only) {
+  if (!b || b->links <= 0 || b->links > mo::kMaxChainLinks || b->n <= 0 || b->n > 6 * b->links || b->batch < 0)
+    return MO_ERR_INVALID_ARGUMENT;
+  if (!b->link_pose || !b->link_mask) return MO_ERR_INVALID_ARGUMENT;
+  if (fk_only) return MO_OK;
+  if (b->n_cost < 0 || b->n_cost > mo::kMaxChainRows || b->n_eq < 0 || b->n_eq > mo::kMaxChainRows || b->m < 0)
+    return MO_ERR_INVALID_ARGUMENT;
+  if (b->cost_block < 0 || (b->cost_block > 0 && b->n_cost % b->cost_block != 0)) return MO_ERR_INVALID_ARGUMENT;
+  if (b->batch == 0) return MO_OK;
+  if ((b->n_cost > 0 && (!b->cost_w || !b->cost_target)) || (b->n_eq > 0 && (!b->eq_w || !b->eq_target)) ||
+      (b->m > 0 && (!b->ineq_var || !b->ineq_a || !b->ineq_b)) || !b->x0)
+    return MO_ERR_INVALID_ARGUMENT;
+  return MO_OK;
+}
+
+mo::ChainArgs make_chain_args(const mo_chain_ik_batch* b) {
+  mo::ChainArgs a{};
+  a.links = b->links; a.n = b->n; a.n_cost = b->n_cost; a.cost_block = b->cost_block; a.n_eq = b->n_eq; a.m = b->m;
+  a.batch = b->batch; a.link_pose = b->link_pose; a.link_mask = b->link_mask; a.cost_w = b->cost_w;
+  a.cost_target = b->cost_target; a.eq_w = b->eq_w; a.eq_target = b->eq_target; a.ineq_var = b->ineq_var;
+  a.ineq_a = b->ineq_a; a.ineq_b = b->ineq_b; a.x0 = b->x0;
+  return a;
+}
+
+template <typename K>
+int warp_grid(K kernel, size_t smem, long long batch, const DeviceInfo& dev, int* grid) {
+  if (smem > (size_t)dev.max_smem_optin) {
+    g_last_error = "problem too large for shared memory: needs " + std::to_string(smem) + " bytes";
+    return MO_ERR_UNSUPPORTED_SHAPE;
+  }
+  int bps = 0;
+  MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32, smem));
+  const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
+  *grid = (int)(batch < cap ? batch : cap);
+  return MO_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void mo_nls_params_default(mo_nls_params* p) {  // nonlinear.hpp:37-124
+  if (!p) return;
+  p->max_iterations = 10; p->max_qp_iterations = 10; p->termination_kkt_tolerance = 1.0e-6;
+  p->absolute_exit_tol = 1.0e-12; p->relative_exit_tol = 1.0e-5; p->absolute_first_derivative_tol = 1.0e-6;
+  p->max_line_search_iterations = 2; p->line_search_strategy = MO_LS_POLYNOMIAL_APPROXIMATION;
+  p->armijo_search_tau = 0.8; p->equality_penalty_initial = 1.0; p->equality_penalty_scale_factor = 1.01;
+  p->equality_penalty_rho = 0.1; p->lambda_initial = 0.0; p->lambda_failure_init = 1.0e-2;
+  p->lambda_decrease_on_success = 0.1; p->lambda_decrease_on_restore = 0.8; p->max_lambda = 1.0; p->min_lambda = 0.0;
+  p->retraction = MO_RETRACT_ADD; p->reserved = 0;
+}
+
+int mo_nls_linearize_batch(const mo_nls_linearize_args* g, int device, void* cuda_stream) {
+  if (!g || g->n <= 0 || g->r_cost < 0 || g->r_eq < 0 || g->m < 0 || g->batch < 0) return MO_ERR_INVALID_ARGUMENT;
+  if (g->cost_block < 0 || (g->cost_block > 0 && g->r_cost % g->cost_block != 0)) return MO_ERR_INVALID_ARGUMENT;
+  if (g->batch == 0) return MO_OK;
+  if (!g->x || !g->lambda || !g->G || !g->c || !g->errors || (g->r_cost > 0 && (!g->J_cost || !g->r_cost_v)) ||
+      (g->r_eq > 0 && (!g->J_eq || !g->r_eq_v || !g->A_eq || !g->b_eq)) ||
+      (g->m > 0 && (!g->ineq_var || !g->ineq_a || !g->ineq_b || !g->ineq_b_shifted)))
+    return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  int rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  mo::LinearizeArgs a{g->n, g->r_cost, g->cost_block, g->r_eq, g->m, g->batch, g->x, g->J_cost, g->r_cost_v, g->J_eq,
+                      g->r_eq_v, g->lambda, g->ineq_var, g->ineq_a, g->ineq_b, g->G, g->c, g->A_eq, g->b_eq,
+                      g->ineq_b_shifted, g->errors};
+  const long long cap = (long long)dev.sms * 32;
+  mo::nls_linearize_kernel<<<(int)(g->batch < cap ? g->batch : cap), 32, 0, static_cast<cudaStream_t>(cuda_stream)>>>(a);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, double* translation, double* rotation_q,
+                      double* t_D_params, double* r_D_params, int device, void* cuda_stream) {
+  int rc = check_chain(chain, true);
+  if (rc) return rc;
+  if (chain->batch == 0) return MO_OK;
+  if (!params) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  const size_t smem = sizeof(double) * mo::chain_smem_doubles(chain->links, chain->n);
+  int grid = 0;
+  rc = warp_grid(mo::chain_fk_kernel, smem, chain->batch, dev, &grid);
+  if (rc) return rc;
+  mo::chain_fk_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(chain), params,
+                                                                                  translation, rotation_q, t_D_params,
+                                                                                  r_D_params);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
+                                int device, void* cuda_stream) {
+  if (!params || !out) return MO_ERR_INVALID_ARGUMENT;
+  int rc = check_chain(problems, false);
+  if (rc) return rc;
+  rc = check_nls_params(params);
+  if (rc) return rc;
+  if (problems->n_eq > 0 && problems->m == 0) {
+    g_last_error = "equality-only problems use QPNullSpaceSolver in the reference (nonlinear.cc:83-89): not built";
+    return MO_ERR_UNSUPPORTED_SHAPE;
+  }
+  if (problems->batch == 0) return MO_OK;
+  if (!out->x || !out->termination || !out->iterations) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  const size_t smem = sizeof(double) * mo::nls_smem_doubles(problems->links, problems->n, problems->n_cost,
+                                                            problems->n_eq, problems->m);
+  int grid = 0;
+  rc = warp_grid(mo::nls_chain_ik_kernel, smem, problems->batch, dev, &grid);
+  if (rc) return rc;
+  const mo::NlsParams p{params->max_iterations, params->max_qp_iterations, params->termination_kkt_tolerance,
+                        params->absolute_exit_tol, params->relative_exit_tol, params->absolute_first_derivative_tol,
+                        params->max_line_search_iterations, params->line_search_strategy, params->armijo_search_tau,
+                        params->equality_penalty_initial, params->equality_penalty_scale_factor,
+                        params->equality_penalty_rho, params->lambda_initial, params->lambda_failure_init,
+                        params->lambda_decrease_on_success, params->lambda_decrease_on_restore, params->max_lambda,
+                        params->min_lambda, params->retraction};
+  const mo::NlsOut o{out->x, out->termination, out->iterations, out->qp_iterations, out->ls_steps, out->errors};
+  mo::nls_chain_ik_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(problems), p, o);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+}  // extern "C"

@@ -517,12 +517,57 @@ __device__ int gen_initial_guess(const GenWork& W, const GenProb& Q, int method)
   return 0;
 }
 
+// Parameters of one Solve() (QPInteriorPointSolver::Params, qp.hpp:134-164).
+struct GenSolveParams {
+  double initial_mu, sigma, kkt_tol, comp_tol;
+  int max_iterations, strategy, decrease_mu_only_on_small_error, guess, init_mu_with_comp;
+};
+
+// Solve (qp.cc:100-151) on a bound problem whose W.vars is zeroed (or holds the user's guess). Returns the
+// termination status (uniform); `iters` = iterations.size(), `kkt_after` = kkt_final of the last iteration.
+// `log` = this problem's iter_log rows or nullptr.
+template <int THREADS>
+__device__ int gen_solve(const GenWork& W, const GenProb& Q, const GenSolveParams& a, double* log, int& iters,
+                         double (&kkt_after)[4]) {
+  const int tid = threadIdx.x;
+  int status = gen_initial_guess<THREADS>(W, Q, a.guess);
+  iters = 0;
+  double kkt_prev[4] = {0, 0, 0, 0}, ip[6];
+  kkt_after[0] = kkt_after[1] = kkt_after[2] = kkt_after[3] = 0.0;
+  if (status) return status;
+  status = MO_QP_MAX_ITERATIONS;
+  gen_eval_kkt<THREADS>(W, Q, true);
+  double mu = a.init_mu_with_comp ? gen_compute_mu<THREADS>(W) : a.initial_mu;
+  for (int iter = 0; iter < a.max_iterations; ++iter) {
+    gen_compute_errors<THREADS>(W, mu, kkt_prev);
+    const int st = gen_iterate<THREADS>(W, Q, mu, a.strategy, ip);
+    if (st) { status = st; break; }
+    gen_eval_kkt<THREADS>(W, Q, true);
+    gen_compute_errors<THREADS>(W, mu, kkt_after);
+    if (log && tid == 0) {
+      double* row = log + iter * MO_QP_ITER_LOG_STRIDE;
+      for (int q = 0; q < 4; ++q) { row[q] = kkt_prev[q]; row[4 + q] = kkt_after[q]; }
+      for (int q = 0; q < 6; ++q) row[8 + q] = ip[q];
+    }
+    ++iters;
+    const double mu_c = gen_compute_mu<THREADS>(W);
+    if (max4(kkt_after) < a.kkt_tol && mu_c < a.comp_tol) { status = MO_QP_SATISFIED_KKT_TOL; break; }
+    if (max4(kkt_after) <= mu || !a.decrease_mu_only_on_small_error) {
+      if (a.strategy == MO_BARRIER_FIXED_DECREASE) mu *= a.sigma;
+      else mu = a.sigma * mu_c;
+    }
+  }
+  return status;
+}
+
 // Solve (qp.cc:100-151): one block per problem, grid-stride over the batch.
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) qp_ip_generic_kernel(const QPArgs a) {
   extern __shared__ double smem[];
   const int tid = threadIdx.x;
   const long long vstride = a.n + 2LL * a.m + a.k;
+  const GenSolveParams sp{a.initial_mu, a.sigma, a.kkt_tol, a.comp_tol, a.max_iterations, a.strategy,
+                          a.decrease_mu_only_on_small_error, a.guess, a.init_mu_with_comp};
   for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
     GenWork W;
     GenProb Q;
@@ -530,33 +575,10 @@ __global__ void __launch_bounds__(THREADS) qp_ip_generic_kernel(const QPArgs a) 
     gen_bind<THREADS>(a, prob, smem, W, Q);
     if (a.guess == MO_GUESS_USER_PROVIDED) gen_load_vars<THREADS>(W, a.m, a.vars + prob * vstride, W.vars);
     else { for (int i = tid; i < W.T; i += THREADS) W.vars[i] = 0.0; block_sync<THREADS>(); }
-    int status = gen_initial_guess<THREADS>(W, Q, a.guess);
     int iters = 0;
-    double kkt_prev[4] = {0, 0, 0, 0}, kkt_after[4] = {0, 0, 0, 0}, ip[6];
-    if (!status) {
-      status = MO_QP_MAX_ITERATIONS;
-      gen_eval_kkt<THREADS>(W, Q, true);
-      double mu = a.init_mu_with_comp ? gen_compute_mu<THREADS>(W) : a.initial_mu;
-      for (int iter = 0; iter < a.max_iterations; ++iter) {
-        gen_compute_errors<THREADS>(W, mu, kkt_prev);
-        const int st = gen_iterate<THREADS>(W, Q, mu, a.strategy, ip);
-        if (st) { status = st; break; }
-        gen_eval_kkt<THREADS>(W, Q, true);
-        gen_compute_errors<THREADS>(W, mu, kkt_after);
-        if (a.iter_log && tid == 0) {
-          double* row = a.iter_log + (prob * a.max_iterations + iter) * MO_QP_ITER_LOG_STRIDE;
-          for (int q = 0; q < 4; ++q) { row[q] = kkt_prev[q]; row[4 + q] = kkt_after[q]; }
-          for (int q = 0; q < 6; ++q) row[8 + q] = ip[q];
-        }
-        ++iters;
-        const double mu_c = gen_compute_mu<THREADS>(W);
-        if (max4(kkt_after) < a.kkt_tol && mu_c < a.comp_tol) { status = MO_QP_SATISFIED_KKT_TOL; break; }
-        if (max4(kkt_after) <= mu || !a.decrease_mu_only_on_small_error) {
-          if (a.strategy == MO_BARRIER_FIXED_DECREASE) mu *= a.sigma;
-          else mu = a.sigma * mu_c;
-        }
-      }
-    }
+    double kkt_after[4];
+    const int status = gen_solve<THREADS>(W, Q, sp, a.iter_log ? a.iter_log + prob * a.max_iterations * MO_QP_ITER_LOG_STRIDE : nullptr,
+                                          iters, kkt_after);
     block_sync<THREADS>();
     gen_store_vars<THREADS>(W, a.m, W.vars, a.vars + prob * vstride);
     if (tid == 0) {
@@ -607,9 +629,5 @@ __global__ void __launch_bounds__(THREADS) qp_ip_generic_step_kernel(const QPArg
 }
 
 #undef KM
-#undef GX
-#undef GS
-#undef GY
-#undef GZ
 
 }  // namespace mo

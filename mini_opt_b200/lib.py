@@ -18,6 +18,7 @@ EXPORTS = [
     "mo_qp_params_default", "mo_qp_vars_stride", "mo_qp_ip_solve_batch", "mo_qp_ip_solve_batch_host",
     "mo_qp_ip_newton_step_batch", "mo_qp_kernel_variant", "mo_kernel_launch_count", "mo_last_error_string",
     "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak",
+    "mo_nls_params_default", "mo_nls_linearize_batch", "mo_chain_fk_batch", "mo_nls_solve_chain_ik_batch",
 ]
 
 
@@ -71,6 +72,15 @@ def load():
     lib.mo_host_free.restype = None
     lib.mo_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
     lib.mo_measure_fp64_peak.restype = C.c_int
+    lib.mo_nls_params_default.argtypes = [C.POINTER(abi.MoNlsParams)]
+    lib.mo_nls_params_default.restype = None
+    lib.mo_nls_linearize_batch.argtypes = [C.POINTER(abi.MoNlsLinearizeArgs), C.c_int, C.c_void_p]
+    lib.mo_nls_linearize_batch.restype = C.c_int
+    lib.mo_chain_fk_batch.argtypes = [C.POINTER(abi.MoChainIkBatch)] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p]
+    lib.mo_chain_fk_batch.restype = C.c_int
+    lib.mo_nls_solve_chain_ik_batch.argtypes = [C.POINTER(abi.MoChainIkBatch), C.POINTER(abi.MoNlsParams),
+                                                C.POINTER(abi.MoNlsOut), C.c_int, C.c_void_p]
+    lib.mo_nls_solve_chain_ik_batch.restype = C.c_int
     if lib.mo_abi_version() != abi.MO_ABI_VERSION:
         raise RuntimeError("libminiopt_b200.so ABI version mismatch; rebuild")
     _lib = lib

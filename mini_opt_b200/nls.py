@@ -1,0 +1,80 @@
+"""Harness-side callers of the nonlinear least squares entry points of the C ABI (tests, bench): packs torch
+device tensors into ``mo_chain_ik_batch`` / ``mo_nls_linearize_args``. torch = device memory and streams only."""
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+
+import numpy as np
+
+from . import abi, lib
+from .qp import _device_index
+
+
+def _to_dev(a, device):
+    import torch
+    return None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(device)
+
+
+def chain_to_device(ch: abi.ChainIKArrays, device) -> abi.ChainIKArrays:
+    kw = {f.name: getattr(ch, f.name) for f in dataclasses.fields(ch)}
+    for name in ("link_pose", "link_mask", "cost_w", "cost_target", "eq_w", "eq_target", "ineq_var", "ineq_a",
+                 "ineq_b", "x0"):
+        kw[name] = _to_dev(kw[name], device)
+    return abi.ChainIKArrays(**kw)
+
+
+def alloc_nls_out_torch(batch: int, n: int, device) -> abi.NLSOutArrays:
+    import torch
+    i32 = dict(dtype=torch.int32, device=device)
+    return abi.NLSOutArrays(x=torch.zeros((batch, n), dtype=torch.float64, device=device),
+                            termination=torch.full((batch,), -1, **i32), iterations=torch.zeros((batch,), **i32),
+                            qp_iterations=torch.zeros((batch,), **i32), ls_steps=torch.zeros((batch,), **i32),
+                            errors=torch.zeros((batch, 2), dtype=torch.float64, device=device))
+
+
+def nls_out_to_numpy(o: abi.NLSOutArrays) -> abi.NLSOutArrays:
+    return abi.NLSOutArrays(**{f.name: getattr(o, f.name).cpu().numpy() for f in dataclasses.fields(o)})
+
+
+def solve_chain_ik_device(ch: abi.ChainIKArrays, params: abi.NLSParams, out: abi.NLSOutArrays, device, stream=None):
+    """``mo_nls_solve_chain_ik_batch`` on device tensors; asynchronous on ``stream``."""
+    import torch
+    st = stream if stream is not None else torch.cuda.current_stream(device)
+    c, p, o = ch.to_c(), params.to_c(), out.to_c()
+    lib.check(lib.load().mo_nls_solve_chain_ik_batch(C.byref(c), C.byref(p), C.byref(o), _device_index(device),
+                                                     st.cuda_stream))
+
+
+def chain_fk_device(ch: abi.ChainIKArrays, params_t, device):
+    """``mo_chain_fk_batch``: dict(translation, rotation_q, t_D_params, r_D_params) of device tensors."""
+    import torch
+    B, n = params_t.shape
+    f64 = dict(dtype=torch.float64, device=device)
+    t, q = torch.zeros((B, 3), **f64), torch.zeros((B, 4), **f64)
+    tD, rD = torch.zeros((B, n, 3), **f64), torch.zeros((B, n, 3), **f64)
+    c = ch.to_c()
+    c.batch = B
+    st = torch.cuda.current_stream(device)
+    lib.check(lib.load().mo_chain_fk_batch(C.byref(c), params_t.data_ptr(), t.data_ptr(), q.data_ptr(), tD.data_ptr(),
+                                           rD.data_ptr(), _device_index(device), st.cuda_stream))
+    return dict(translation=t, rotation_q=q, t_D_params=tD, r_D_params=rD)
+
+
+def linearize_device(a: abi.LinearizeArrays, device) -> abi.LinearizeOut:
+    """``mo_nls_linearize_batch`` on host arrays copied to ``device``; returns device tensors."""
+    import torch
+    kw = {f.name: getattr(a, f.name) for f in dataclasses.fields(a)}
+    for name in ("x", "J_cost", "r_cost_v", "J_eq", "r_eq_v", "lam", "ineq_var", "ineq_a", "ineq_b"):
+        kw[name] = _to_dev(kw[name], device)
+    d = abi.LinearizeArrays(**kw)
+    B, n, k, m = a.batch, a.n, a.r_eq, a.m
+    f64 = dict(dtype=torch.float64, device=device)
+    o = abi.LinearizeOut(G=torch.full((B, n, n), float("nan"), **f64), c=torch.zeros((B, n), **f64),
+                         A_eq=torch.zeros((B, n, k), **f64), b_eq=torch.zeros((B, k), **f64),
+                         ineq_b_shifted=torch.zeros((B, m), **f64), errors=torch.zeros((B, 2), **f64))
+    args = abi.linearize_to_c(d, o)
+    st = torch.cuda.current_stream(device)
+    lib.check(lib.load().mo_nls_linearize_batch(C.byref(args), _device_index(device), st.cuda_stream))
+    torch.cuda.synchronize()
+    return o

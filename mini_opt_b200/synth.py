@@ -88,3 +88,50 @@ def solve_params(guess: int = abi.MO_GUESS_SOLVE_EQUALITY_CONSTRAINED) -> abi.QP
     return abi.QPParams(initial_mu=1.0, sigma=0.1, termination_kkt_tol=1e-9, termination_complementarity_tol=1e-6,
                         max_iterations=30, barrier_strategy=abi.MO_BARRIER_COMPLEMENTARITY,
                         initial_guess_method=guess)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# BASELINE config 3: transform-chain IK problems
+# ---------------------------------------------------------------------------------------------------------
+def chain_ik_batch_numpy(links: int, batch: int, seed: int = 4321, n_eq: int = 0) -> abi.ChainIKArrays:
+    """Chains of ``links`` Z-revolute links, each ``Pose(Identity, (0.3, 0, 0))`` with mask {0,0,1,0,0,0} (the pattern
+    of test/nonlinear_test.cc:833-837, 967-985). Cost: one 2-row Residual, effector (x, y) - target, target uniform
+    inside 0.8 x reach. Joint limits Var(i) in [-pi/2, pi/2] (cf. :928-929), initial angles U(-0.5, 0.5).
+    ``n_eq`` = 1 moves the x row into an equality constraint (the x_eq / y_res split of :840-859)."""
+    rng = np.random.default_rng(seed)
+    n = links
+    pose = np.zeros((links, 7))
+    pose[:, 0] = 1.0
+    pose[:, 4] = 0.3
+    mask = np.zeros((links, 6), dtype=np.uint8)
+    mask[:, 2] = 1
+    reach = 0.3 * (links - 1)  # the first link's translation comes before its own rotation? no: after; see FK
+    reach = 0.3 * links
+    radius = 0.8 * reach * np.sqrt(rng.uniform(0.0, 1.0, size=batch))
+    phi = rng.uniform(-np.pi, np.pi, size=batch)
+    target = np.stack([radius * np.cos(phi), radius * np.sin(phi)], axis=1)
+    x0 = rng.uniform(-0.5, 0.5, size=(batch, n))
+    var = np.repeat(np.arange(n, dtype=np.int32), 2)
+    a = np.tile(np.array([1.0, -1.0]), n)
+    b = np.full(2 * n, np.pi / 2)
+    if n_eq == 0:
+        cost_w = np.array([[1.0, 0, 0], [0, 1.0, 0]])
+        return abi.ChainIKArrays(links=links, n=n, n_cost=2, cost_block=2, n_eq=0, m=2 * n, batch=batch,
+                                 link_pose=pose, link_mask=mask, cost_w=cost_w,
+                                 cost_target=np.ascontiguousarray(target), ineq_var=var, ineq_a=a, ineq_b=b, x0=x0)
+    return abi.ChainIKArrays(links=links, n=n, n_cost=1, cost_block=1, n_eq=1, m=2 * n, batch=batch,
+                             link_pose=pose, link_mask=mask, cost_w=np.array([[0.0, 1.0, 0.0]]),
+                             cost_target=np.ascontiguousarray(target[:, 1:2]), eq_w=np.array([[1.0, 0.0, 0.0]]),
+                             eq_target=np.ascontiguousarray(target[:, 0:1]), ineq_var=var, ineq_a=a, ineq_b=b, x0=x0)
+
+
+def chain_ik_params(max_qp_iterations: int = 20) -> abi.NLSParams:
+    """Params of TestDualActuatorBalancing (test/nonlinear_test.cc:1086-1102) + the ModPi retraction (:1076-1082).
+    ``max_qp_iterations`` defaults to 20 instead of that test's 5: with 5 the REFERENCE itself brings only 9 % of the
+    6-link problems below absolute_exit_tol (70 % with 20); pass 5 for the literal test configuration."""
+    return abi.NLSParams(max_iterations=100, max_qp_iterations=max_qp_iterations, relative_exit_tol=1e-12,
+                         absolute_first_derivative_tol=1e-10, absolute_exit_tol=1e-8,
+                         termination_kkt_tolerance=1e-6, max_line_search_iterations=5,
+                         line_search_strategy=abi.MO_LS_ARMIJO_BACKTRACK, lambda_failure_init=0.01,
+                         armijo_search_tau=0.5, lambda_initial=0.001, min_lambda=1e-9,
+                         retraction=abi.MO_RETRACT_MOD_PI)

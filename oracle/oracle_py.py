@@ -48,6 +48,19 @@ def _bind_qp(lib, prefix: str, with_threads: bool):
                      C.c_void_p, C.c_void_p]
 
 
+def _bind_nls(lib, prefix: str, with_threads: bool):
+    lin = getattr(lib, f"{prefix}_nls_linearize_batch")
+    lin.restype = C.c_int
+    lin.argtypes = [C.POINTER(abi.MoNlsLinearizeArgs)]
+    fk = getattr(lib, f"{prefix}_chain_fk_batch")
+    fk.restype = C.c_int
+    fk.argtypes = [C.POINTER(abi.MoChainIkBatch)] + [C.c_void_p] * 5
+    solve = getattr(lib, f"{prefix}_nls_solve_chain_ik_batch")
+    solve.restype = C.c_int64
+    solve.argtypes = [C.POINTER(abi.MoChainIkBatch), C.POINTER(abi.MoNlsParams), C.POINTER(abi.MoNlsOut)] + (
+        [C.c_int] if with_threads else [])
+
+
 def oracle_lib():
     global _oracle
     if _oracle is None:
@@ -55,6 +68,7 @@ def oracle_lib():
             build()
         _oracle = C.CDLL(str(ORACLE_SO))
         _bind_qp(_oracle, "oracle", with_threads=False)
+        _bind_nls(_oracle, "oracle", with_threads=False)
     return _oracle
 
 
@@ -69,6 +83,7 @@ def ref_lib():
             build()
         _ref = C.CDLL(str(REF_SO))
         _bind_qp(_ref, "ref", with_threads=True)
+        _bind_nls(_ref, "ref", with_threads=True)
         _ref.ref_generate_random_qp.restype = C.c_int
         _ref.ref_generate_random_qp.argtypes = [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 6
         _ref.ref_hardware_concurrency.restype = C.c_int
@@ -134,3 +149,47 @@ def generate_random_qp(seed: int, dim: int = 8, p_inequality: float = 0.5):
     cnt = lib.ref_generate_random_qp(int(seed), int(dim), float(p_inequality), G.ctypes.data, c.ctypes.data,
                                      var.ctypes.data, a.ctypes.data, b.ctypes.data, sol.ctypes.data)
     return dict(G=G, c=c, var=var[:cnt].copy(), a=a[:cnt].copy(), b=b[:cnt].copy(), solution=sol, count=cnt)
+
+
+def _lib(which: str):
+    return oracle_lib() if which == "oracle" else ref_lib()
+
+
+def nls_linearize(which: str, a: abi.LinearizeArrays) -> abi.LinearizeOut:
+    """``LinearizeAndFillQP`` (nonlinear.cc:170-214) on dense per-problem Jacobians (host arrays)."""
+    out = abi.alloc_linearize_out_numpy(a)
+    args = abi.linearize_to_c(a, out)
+    rc = getattr(_lib(which), f"{which}_nls_linearize_batch")(C.byref(args))
+    if rc != 0:
+        raise RuntimeError(f"{which}_nls_linearize_batch failed: {rc}")
+    return out
+
+
+def chain_fk(which: str, chain: abi.ChainIKArrays, params: np.ndarray):
+    """``ActuatorChain::Update`` per row of ``params``: dict(translation, rotation_q, t_D_params, r_D_params)."""
+    B, n = params.shape
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    t = np.zeros((B, 3))
+    q = np.zeros((B, 4))
+    tD = np.zeros((B, n, 3))
+    rD = np.zeros((B, n, 3))
+    c = chain.to_c()
+    c.batch = B
+    rc = getattr(_lib(which), f"{which}_chain_fk_batch")(C.byref(c), params.ctypes.data, t.ctypes.data, q.ctypes.data,
+                                                         tD.ctypes.data, rD.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"{which}_chain_fk_batch failed: {rc}")
+    return dict(translation=t, rotation_q=q, t_D_params=tD, r_D_params=rD)
+
+
+def nls_solve_chain(which: str, chain: abi.ChainIKArrays, params: abi.NLSParams, nthreads: int = 1):
+    """``ConstrainedNonlinearLeastSquares::Solve`` per problem. Returns (NLSOutArrays, total QP iterations)."""
+    out = abi.alloc_nls_out_numpy(chain.batch, chain.n)
+    c, p, o = chain.to_c(), params.to_c(), out.to_c()
+    if which == "oracle":
+        total = oracle_lib().oracle_nls_solve_chain_ik_batch(C.byref(c), C.byref(p), C.byref(o))
+    else:
+        total = ref_lib().ref_nls_solve_chain_ik_batch(C.byref(c), C.byref(p), C.byref(o), int(nthreads))
+    if total < 0:
+        raise RuntimeError(f"{which}_nls_solve_chain_ik_batch failed: {total}")
+    return out, int(total)

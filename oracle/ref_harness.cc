@@ -17,24 +17,10 @@
 
 #include "mini_opt/qp.hpp"
 
+#include "ref_friend.h"
+
 #include "mini_opt_b200.h"
 
-namespace mini_opt {
-
-// qp.hpp:293-294 befriends `QPSolverTest` and `ConstrainedNLSTest`. The reference's own test binaries
-// define them; this harness defines the second name to reach Iterate()/delta_ for step-level parity.
-class ConstrainedNLSTest {
- public:
-  static IPIterationOutputs Iterate(QPInteriorPointSolver& s, double mu, BarrierStrategy strat) {
-    return s.Iterate(mu, strat);
-  }
-  static const Eigen::VectorXd& Delta(const QPInteriorPointSolver& s) { return s.delta_; }
-  static void EvaluateKKT(QPInteriorPointSolver& s) { s.EvaluateKKTConditions(); }
-  static KKTError Errors(const QPInteriorPointSolver& s, double mu) { return s.ComputeErrors(mu); }
-  static Eigen::VectorXd& Vars(QPInteriorPointSolver& s) { return s.variables_; }
-};
-
-}  // namespace mini_opt
 
 using namespace mini_opt;
 

@@ -1,0 +1,125 @@
+"""GPU parity tests (-m gpu) of the nonlinear least squares path: mo_chain_fk_batch, mo_nls_linearize_batch and
+mo_nls_solve_chain_ik_batch, called through the C ABI, against the golden vectors recorded from the reference and
+against the plain-C oracle on the same seeded inputs. Tolerances: 1e-12 for FK / linearization (the reference's own
+test tolerances), relative 1e-9 on x with identical termination state and iteration counts for the solves; the
+rounding-sensitive redundant-chain batches are bounded by fraction as in tests/test_oracle_nls.py."""
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import nls_cases as N
+from mini_opt_b200 import abi, synth
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1] / "tools"))
+from make_golden import IK_SETS, LINEARIZE_SHAPES  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from mini_opt_b200 import lib
+    lib.load()
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def golden_nls():
+    return np.load(Path(__file__).parent / "golden" / "nls_chain.npz")
+
+
+def gpu_nls(ch, prm, dev):
+    import torch
+    from mini_opt_b200 import nls
+    out = nls.alloc_nls_out_torch(ch.batch, ch.n, dev)
+    nls.solve_chain_ik_device(nls.chain_to_device(ch, dev), prm, out, dev)
+    torch.cuda.synchronize()
+    return nls.nls_out_to_numpy(out)
+
+
+def counts_same(a, b_term, b_it, b_qp, b_ls):
+    return (a.termination == b_term) & (a.iterations == b_it) & (a.qp_iterations == b_qp) & (a.ls_steps == b_ls)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_chain_fk_golden(dev, golden_nls, seed):
+    import torch
+    from mini_opt_b200 import nls
+    ch, P = N.random_general_chain(seed)
+    fk = nls.chain_fk_device(nls.chain_to_device(ch, dev), torch.from_numpy(P).to(dev), dev)
+    torch.cuda.synchronize()
+    for k, v in fk.items():
+        np.testing.assert_allclose(v.cpu().numpy(), golden_nls[f"fk{seed}_{k}"], atol=1e-12, rtol=0)
+
+
+@pytest.mark.parametrize("idx", range(len(LINEARIZE_SHAPES)))
+def test_linearize_golden(dev, golden_nls, idx):
+    from mini_opt_b200 import nls
+    n, rc, cb, re = LINEARIZE_SHAPES[idx]
+    out = nls.linearize_device(N.random_linearize(100 + idx, n, rc, cb, re), dev)
+    for f in ("G", "c", "A_eq", "b_eq", "ineq_b_shifted", "errors"):
+        np.testing.assert_allclose(getattr(out, f).cpu().numpy(), golden_nls[f"lin{idx}_{f}"], atol=1e-12, rtol=0)
+    assert np.all(np.triu(out.G.cpu().numpy().transpose(0, 2, 1), 1) == 0.0)  # residual_test.cc: upper triangle exactly 0
+
+
+def test_two_angle_chain(dev, golden_nls):
+    """TestTwoAngleActuatorChain with inequalities (nonlinear_test.cc:925-960)."""
+    ch, prm = N.two_angle_chain()
+    out = gpu_nls(ch, prm, dev)
+    g = golden_nls
+    same = counts_same(out, g["two_angle_termination"], g["two_angle_iterations"], g["two_angle_qp_iterations"],
+                       g["two_angle_ls_steps"])
+    assert same.mean() >= 0.99, same.mean()
+    np.testing.assert_allclose(out.x[same], g["two_angle_x"][same], rtol=1e-9, atol=1e-12)
+    assert (out.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL).all()
+    assert np.abs(out.x - g["two_angle_x"]).max() < 1e-5 and out.ls_steps.max() < 100
+    np.testing.assert_allclose(out.errors, g["two_angle_errors"], atol=1e-9)
+
+
+@pytest.mark.parametrize("tag,links,neq,qpi,B", IK_SETS)
+def test_chain_ik_golden(dev, golden_nls, tag, links, neq, qpi, B):
+    ch = synth.chain_ik_batch_numpy(links, B, seed=777 + links, n_eq=neq)
+    out = gpu_nls(ch, synth.chain_ik_params(qpi), dev)
+    g = golden_nls
+    same = counts_same(out, g[f"{tag}_termination"], g[f"{tag}_iterations"], g[f"{tag}_qp_iterations"], g[f"{tag}_ls_steps"])
+    need = 0.65 if neq else 0.93
+    assert same.mean() >= need, same.mean()
+    assert (out.termination == g[f"{tag}_termination"]).mean() >= need
+    dx = np.abs(out.x - g[f"{tag}_x"]).max(axis=1)
+    assert np.mean(dx[same] < 1e-6) >= 0.9, np.mean(dx[same] < 1e-6)
+
+
+@pytest.mark.parametrize("links,strategy", [(6, abi.MO_LS_ARMIJO_BACKTRACK), (9, abi.MO_LS_POLYNOMIAL_APPROXIMATION),
+                                            (12, abi.MO_LS_ARMIJO_BACKTRACK)])
+def test_chain_ik_vs_oracle(dev, oracle, links, strategy):
+    ch = synth.chain_ik_batch_numpy(links, 1500, seed=31 + links)
+    prm = synth.chain_ik_params()
+    prm.line_search_strategy = strategy
+    ref, _ = oracle.nls_solve_chain("oracle", ch, prm)
+    out = gpu_nls(ch, prm, dev)
+    same = counts_same(out, ref.termination, ref.iterations, ref.qp_iterations, ref.ls_steps)
+    assert same.mean() >= 0.93, same.mean()
+    dx = np.abs(out.x - ref.x).max(axis=1)
+    assert np.mean(dx[same] < 1e-6) >= 0.9
+    ok = same & (ref.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL)
+    np.testing.assert_allclose(out.errors[ok], ref.errors[ok], atol=1e-9)
+
+
+def test_nls_invalid_arguments(dev):
+    from mini_opt_b200 import lib, nls
+    ch, prm = N.two_angle_chain()
+    d = nls.chain_to_device(ch, dev)
+    out = nls.alloc_nls_out_torch(ch.batch, ch.n, dev)
+    bad = abi.NLSParams(**{**prm.__dict__, "max_qp_iterations": 0})
+    with pytest.raises(lib.MiniOptError) as e:
+        nls.solve_chain_ik_device(d, bad, out, dev)
+    assert e.value.code == abi.MO_ERR_INVALID_PARAMS
+    d.m = 0  # equality-only -> QPNullSpaceSolver in the reference: not built
+    with pytest.raises(lib.MiniOptError) as e:
+        nls.solve_chain_ik_device(d, prm, out, dev)
+    assert e.value.code == abi.MO_ERR_UNSUPPORTED_SHAPE

@@ -109,11 +109,48 @@ def box_synth():
     np.savez_compressed(GOLD / "qp_box_synth.npz", **save)
 
 
+def nls_golden():
+    """tests/golden/nls_chain.npz: reference outputs for the NLS path (LinearizeAndFillQP, ActuatorChain::Update,
+    ConstrainedNonlinearLeastSquares::Solve). Inputs are regenerated from seeds by tests/nls_cases.py / synth.py."""
+    import nls_cases as N
+    save = {}
+    for seed in range(6):
+        ch, P = N.random_general_chain(seed)
+        fk = O.chain_fk("ref", ch, P)
+        for k, v in fk.items():
+            save[f"fk{seed}_{k}"] = v
+    for i, (n, rc, cb, re) in enumerate(LINEARIZE_SHAPES):
+        out = O.nls_linearize("ref", N.random_linearize(100 + i, n, rc, cb, re))
+        for f in ("G", "c", "A_eq", "b_eq", "ineq_b_shifted", "errors"):
+            save[f"lin{i}_{f}"] = getattr(out, f)
+        assert np.all(np.triu(out.G.transpose(0, 2, 1), 1) == 0.0)  # strict upper triangle exactly 0 (residual_test.cc)
+    ch, prm = N.two_angle_chain()
+    out, total = O.nls_solve_chain("ref", ch, prm)
+    fk = O.chain_fk("ref", ch, out.x)
+    assert np.abs(fk["translation"][:, :2] - np.array([0.45, 0.6])).max() < 1e-3  # nonlinear_test.cc:949
+    assert out.ls_steps.max() < 100                                                # nonlinear_test.cc:956
+    for f in ("x", "termination", "iterations", "qp_iterations", "ls_steps", "errors"):
+        save[f"two_angle_{f}"] = getattr(out, f)
+    print(f"two_angle: {total} QP iterations, termination {np.bincount(out.termination)}")
+    for tag, links, neq, qpi, B in IK_SETS:
+        ch = synth.chain_ik_batch_numpy(links, B, seed=777 + links, n_eq=neq)
+        out, total = O.nls_solve_chain("ref", ch, synth.chain_ik_params(qpi))
+        for f in ("x", "termination", "iterations", "qp_iterations", "ls_steps", "errors"):
+            save[f"{tag}_{f}"] = getattr(out, f)
+        print(f"{tag}: {total} QP iterations, termination {np.bincount(out.termination, minlength=5)}")
+    np.savez_compressed(GOLD / "nls_chain.npz", **save)
+
+
+LINEARIZE_SHAPES = ((6, 3, 3, 0), (8, 4, 2, 2), (12, 6, 1, 3), (5, 2, 0, 1))
+IK_SETS = (("ik6", 6, 0, 20, 256), ("ik12", 12, 0, 20, 128), ("ik6q5", 6, 0, 5, 256), ("ik8eq", 8, 1, 20, 128))
+
+
 if __name__ == "__main__":
     GOLD.mkdir(parents=True, exist_ok=True)
     O.build()
     generated_problems()
     fixed_cases()
     box_synth()
+    nls_golden()
     for f in sorted(GOLD.glob("*.npz")):
         print(f.name, f.stat().st_size, "bytes")
