@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 
+#include "qp_dmma.cuh"
 #include "qp_generic.cuh"
 #include "qp_tpp.cuh"
 
@@ -168,6 +169,39 @@ bool tpp_eligible(int n, int k, int m, int flags, bool ragged, int strategy) {
   return false;
 }
 
+// (N, K, warps per CTA, min CTAs per SM) shapes with a DMMA CTA-per-problem instantiation (box pairs, m == 2n).
+#define MO_DM_SHAPES(X) X(64, 16, 4, 5) X(32, 8, 2, 8) X(16, 8, 1, 16)
+
+template <int N, int K, int W, int MINB>
+int launch_dm(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
+  using L = mo::DmLayout<N, K, W>;
+  auto kernel = mo::qp_dm_kernel<N, K, W, MINB>;
+  static thread_local int configured_dev = -1;
+  static thread_local int bps = 0;
+  int cur = 0;
+  MO_CUDA(cudaGetDevice(&cur));
+  if (configured_dev != cur) {
+    MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, L::THREADS, L::SMEM_BYTES));
+    if (bps < 1) { g_last_error = "dm kernel does not fit on an SM"; return MO_ERR_UNSUPPORTED_SHAPE; }
+    configured_dev = cur;
+  }
+  const long long cap = (long long)dev.sms * bps;
+  kernel<<<(int)(a.batch < cap ? a.batch : cap), L::THREADS, L::SMEM_BYTES, stream>>>(a);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+bool dm_eligible(int n, int k, int m, int flags, bool ragged, int strategy) {
+  if (!(flags & MO_QP_FLAG_BOX_PAIRS) || ragged || m != 2 * n) return false;
+  if (strategy == MO_BARRIER_PREDICTOR_CORRECTOR) return false;
+#define X(N_, K_, W_, B_) if (n == N_ && k == K_) return true;
+  MO_DM_SHAPES(X)
+#undef X
+  return false;
+}
+
 int generic_threads(int n, int k) {
   const int p = n + k;
   return p <= 32 ? 32 : (p <= 64 ? 128 : 256);
@@ -218,6 +252,11 @@ int dispatch_solve(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stre
     MO_TPP_SHAPES(X)
 #undef X
   }
+  if (vec_ok && dm_eligible(a.n, a.k, a.m, a.flags, a.icount != nullptr, a.strategy)) {
+#define X(N_, K_, W_, B_) if (a.n == N_ && a.k == K_) return launch_dm<N_, K_, W_, B_>(a, dev, stream);
+    MO_DM_SHAPES(X)
+#undef X
+  }
   return dispatch_generic(a, nullptr, dev, stream);
 }
 
@@ -252,6 +291,7 @@ const char* mo_last_error_string(void) { return g_last_error.c_str(); }
 
 const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags) {
   if (tpp_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY)) return "tpp";
+  if (dm_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY)) return "dmma";
   switch (generic_threads(n, k)) {
     case 32: return "generic32";
     case 128: return "generic128";

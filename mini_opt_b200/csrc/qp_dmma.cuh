@@ -1,0 +1,582 @@
+// CTA-per-problem interior point QP solve for medium dense box-constrained QPs (n, k multiples of 8, n + k <= 80)
+// with the O(p^3) work on the FP64 tensor path: mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4).
+//
+// Replaces, for every problem of a batch: QPInteriorPointSolver::Setup + Solve (source/qp.cc:20-73, 100-151):
+// ComputeInitialGuess (:439-482), the Iterate loop (:153-201), EvaluateKKTConditions (:391-420), ComputeLDLT
+// (:275-316) + SolveForUpdate (:318-364) as ONE unpivoted LDL' factorization and ONE two-sided solve (no explicit
+// inverse), ComputeAlpha (:485-507), ComputeMu (:509-516), ComputeErrors (:423-437).
+//
+// Mapping (P = n + k, NT = P/8 tile rows, W warps per CTA):
+//   * The reduced KKT matrix [[G + Sigma, A'],[A, 0]] (lower triangle, 8x8 tiles) lives in DMMA ACCUMULATOR
+//     fragments: tile row I belongs to warp rowwarp(I) (snake order, balanced as the factorization shrinks).
+//   * Right-looking LDL' over 8-column panels. Per panel: owners spill the panel's tiles to shared memory; one warp
+//     factors the 8x8 diagonal block (lane = row, shuffles); one THREAD per panel row does the triangular solve and
+//     writes L in a 4-column "chunk" layout whose rows are exactly the DMMA A/B fragment order (conflict-free LDS.64);
+//     the trailing update is 2 DMMAs per tile, A fragments shared along a tile row.
+//   * The right-hand side rides along as an extra row of the panel, so the forward substitution is free; the back
+//     substitution runs block by block from L in shared memory.
+//   * G and A_eq are re-staged into shared memory once per Newton step with cp.async (they stay L2-resident for the
+//     life of the problem) into the region L will overwrite: packed trapezoid columns padded so that both the
+//     fragment loads and the thread-per-row symmetric matvec are bank-conflict free.
+#pragma once
+
+#include "qp_common.cuh"
+
+namespace mo {
+
+template <int N, int K, int W>
+struct DmLayout {
+  static constexpr int P = N + K, NT = P / 8, NTN = N / 8, M = 2 * N, THREADS = 32 * W;
+  static_assert(N % 8 == 0 && K % 8 == 0 && N > 0, "tile shapes");
+  static_assert(P <= THREADS, "one thread per KKT row");
+  static_assert(2 * N <= 4 * THREADS, "matvec task split");
+  __host__ __device__ static constexpr int rowwarp(int I) {
+    const int idx = NT - 1 - I, r = idx % (2 * W);
+    return r < W ? r : 2 * W - 1 - r;
+  }
+  __host__ __device__ static constexpr int slotbase(int I) {
+    int s = 0;
+    for (int i = 0; i < I; ++i)
+      if (rowwarp(i) == rowwarp(I)) s += i + 1;
+    return s;
+  }
+  __host__ __device__ static constexpr int maxslots() {
+    int best = 0;
+    for (int w = 0; w < W; ++w) {
+      int s = 0;
+      for (int i = 0; i < NT; ++i)
+        if (rowwarp(i) == w) s += i + 1;
+      best = s > best ? s : best;
+    }
+    return best;
+  }
+  // L in 4-column chunks: chunk kc holds columns 4kc..4kc+3 of rows 8*(kc/2) .. P-1, row-major [row][4], +4 pad
+  __host__ __device__ static constexpr int chunk_off(int kc) {
+    const int j = kc / 2;
+    return 8 * j * (P + 1) - 32 * j * (j - 1) + ((kc & 1) ? (P - 8 * j) * 4 + 4 : 0);
+  }
+  static constexpr int LSIZE = chunk_off(2 * NT);
+  // staged G: column c (rows >= 8*(c/8)) of length N - 8*(c/8) + 2
+  __host__ __device__ static constexpr int gcol_off(int c) {
+    const int jb = c / 8;
+    return 8 * (jb * (N + 2) - 4 * jb * (jb - 1)) + (c % 8) * (N - 8 * jb + 2);
+  }
+  static constexpr int GSIZE = gcol_off(N);
+  static constexpr int ALD = K + 2;
+  static constexpr int ASIZE = K > 0 ? N * ALD : 0;
+  static constexpr int REGION = (LSIZE > GSIZE + ASIZE ? LSIZE : GSIZE + ASIZE) + 2;
+  static constexpr int PLD = 10;  // row stride of the raw panel buffer
+  // shared memory map (doubles)
+  static constexpr int O_REGION = 0;
+  static constexpr int O_PRAW = O_REGION + REGION;
+  static constexpr int O_DJ = O_PRAW + P * PLD;       // d[8], dinv[8], rhs exchange [8], w (unscaled) [8]
+  static constexpr int O_X = O_DJ + 32;
+  static constexpr int O_Y = O_X + N;
+  static constexpr int O_S = O_Y + (K > 0 ? K : 2);
+  static constexpr int O_Z = O_S + M;
+  static constexpr int O_C = O_Z + M;
+  static constexpr int O_B = O_C + N;
+  static constexpr int O_IB = O_B + (K > 0 ? K : 2);
+  static constexpr int O_SIG = O_IB + M;              // Sigma_v = z0/s0 + z1/s1
+  static constexpr int O_T1 = O_SIG + N;              // matvec partials / base
+  static constexpr int O_T2 = O_T1 + N;
+  static constexpr int O_RPE = O_T2 + N;
+  static constexpr int O_DALL = O_RPE + (K > 0 ? K : 2);  // all pivots d[P]
+  static constexpr int O_WP = O_DALL + P;             // forward-solved, D^-1-scaled rhs
+  static constexpr int O_SOL = O_WP + P;              // solution [dx; -dy]
+  static constexpr int O_RED = O_SOL + P;             // reductions: 8 values x W warps (+ flags)
+  static constexpr int TOTAL = O_RED + 8 * W + 8;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
+};
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(c0), "+d"(c1)
+      : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Reciprocal with a 3-deep dependent chain: x(1 + e + e^2), e = 1 - d x  (|e| ~ 2^-23 after MUFU.RCP64H + one step
+// folded in): full double accuracy for normal d.
+__device__ __forceinline__ double rcp_chain(double d) {
+  double x;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
+  const double e = fma(-d, x, 1.0);
+  const double p = fma(e, e, e);
+  x = fma(x, p, x);
+  const double e2 = fma(-d, x, 1.0);
+  return fma(x, e2, x);
+}
+
+// Sum / min over the CTA of NV values per thread; result broadcast to every thread. `red` holds NV*W doubles.
+template <int W, int NV, bool IS_MIN>
+__device__ __forceinline__ void block_reduce(double (&v)[NV], double* red) {
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double t = __shfl_xor_sync(0xffffffffu, v[i], o);
+      v[i] = IS_MIN ? fmin(v[i], t) : v[i] + t;
+    }
+  if (W == 1) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0)
+#pragma unroll
+    for (int i = 0; i < NV; ++i) red[warp * NV + i] = v[i];
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    double t = red[i];
+#pragma unroll
+    for (int w = 1; w < W; ++w) t = IS_MIN ? fmin(t, red[w * NV + i]) : t + red[w * NV + i];
+    v[i] = t;
+  }
+}
+
+// cp.async staging of the problem's G (lower trapezoid) and A_eq into the region L will later overwrite.
+template <int N, int K, int W>
+__device__ __forceinline__ void dm_stage_issue(double* __restrict__ region, const double* __restrict__ Gp,
+                                               const double* __restrict__ Ap) {
+  using L = DmLayout<N, K, W>;
+  constexpr int HG = N / 2;
+  for (int task = threadIdx.x; task < N * HG; task += L::THREADS) {
+    const int c = task / HG, row = 2 * (task - c * HG), rb = 8 * (c / 8);
+    if (row >= rb) cp_async16(region + L::gcol_off(c) + row - rb, Gp + c * N + row);
+  }
+  if (K > 0) {
+    constexpr int HA = K / 2;
+    for (int task = threadIdx.x; task < N * HA; task += L::THREADS) {
+      const int c = task / HA, row = 2 * (task - c * HA);
+      cp_async16(region + L::GSIZE + c * L::ALD + row, Ap + c * K + row);
+    }
+  }
+  cp_async_commit();
+}
+
+// Reduced KKT matrix [[G + Sigma, .],[A, 0]] (ComputeLDLT assembly, qp.cc:289-297) into accumulator fragments.
+template <int N, int K, int W, int MAXS>
+__device__ __forceinline__ void dm_assemble(double (&acc)[MAXS][2], const double* __restrict__ sm, bool with_sigma) {
+  using L = DmLayout<N, K, W>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, r = lane >> 2, q = lane & 3;
+  const double* __restrict__ region = sm + L::O_REGION;
+#pragma unroll
+  for (int I = 0; I < L::NT; ++I) {
+    if (L::rowwarp(I) != warp) continue;
+#pragma unroll
+    for (int J = 0; J <= I; ++J) {
+      const int slot = L::slotbase(I) + J;
+      double c0 = 0.0, c1 = 0.0;
+      if (I < L::NTN) {
+        constexpr int dummy = 0; (void)dummy;
+        const int len = N - 8 * J + 2;
+        const int base = L::gcol_off(8 * J) + 8 * (I - J) + r;
+        c0 = region[base + (2 * q) * len];
+        c1 = region[base + (2 * q + 1) * len];
+        if (I == J && with_sigma) {
+          const double sg = sm[L::O_SIG + 8 * I + r];
+          if (r == 2 * q) c0 += sg;
+          if (r == 2 * q + 1) c1 += sg;
+        }
+      } else if (J < L::NTN) {
+        const int base = L::GSIZE + 8 * (I - L::NTN) + r;
+        c0 = region[base + (8 * J + 2 * q) * L::ALD];
+        c1 = region[base + (8 * J + 2 * q + 1) * L::ALD];
+      }
+      acc[slot][0] = c0;
+      acc[slot][1] = c1;
+    }
+  }
+}
+
+// Unpivoted LDL' of the matrix held in `acc` (right-looking, 8-column panels, DMMA trailing updates) fused with the
+// forward substitution of the right-hand side `racc` (thread t < P holds entry t), then the back substitution.
+// On return sm[O_SOL .. O_SOL+P) = K^-1 rhs for every thread to read. Returns false (uniformly) on a zero or
+// non-finite pivot (-> MO_QP_FAILED_FACTORIZATION, the batched stand-in for the exception of qp.cc:303-307).
+template <int N, int K, int W, int MAXS>
+__device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double racc, double* __restrict__ sm) {
+  using L = DmLayout<N, K, W>;
+  constexpr int P = L::P, NT = L::NT, PLD = L::PLD;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = lane >> 2, q = lane & 3;
+  double* __restrict__ Lch = sm + L::O_REGION;
+  double* __restrict__ praw = sm + L::O_PRAW;
+  double* __restrict__ dj = sm + L::O_DJ;
+  int* failflag = reinterpret_cast<int*>(sm + L::O_RED + 8 * W);
+  if (tid == 0) *failflag = 0;
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    // ---- P1: spill panel column j (raw values) and the right-hand side entries of block j ----
+#pragma unroll
+    for (int I = j; I < NT; ++I) {
+      if (L::rowwarp(I) != warp) continue;
+      const int slot = L::slotbase(I) + j;
+      *reinterpret_cast<double2*>(praw + (8 * I + r) * PLD + 2 * q) = make_double2(acc[slot][0], acc[slot][1]);
+    }
+    if (tid >= 8 * j && tid < 8 * j + 8) dj[16 + tid - 8 * j] = racc;
+    __syncthreads();
+    // ---- P2: LDL' of the 8x8 diagonal block: lane = row, column by column, shuffles ----
+    if (warp == j % W) {
+      const int lr = lane & 7;
+      double a[8];
+#pragma unroll
+      for (int c = 0; c < 8; c += 2) {
+        const double2 v = *reinterpret_cast<const double2*>(praw + (8 * j + lr) * PLD + c);
+        a[c] = v.x; a[c + 1] = v.y;
+      }
+      bool ok = true;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const double dc = __shfl_sync(0xffffffffu, a[c], c);
+        ok = ok && (fabs(dc) > 0.0) && (fabs(dc) <= 1.7976931348623157e308);
+        const double inv = rcp_chain(dc);
+        const double uc = a[c];
+        const double lc = uc * inv;
+#pragma unroll
+        for (int c2 = c + 1; c2 < 8; ++c2) {
+          const double v = __shfl_sync(0xffffffffu, uc, c2);
+          a[c2] = fma(-lc, v, a[c2]);
+        }
+        if (lane == c) { dj[c] = dc; dj[8 + c] = inv; sm[L::O_DALL + 8 * j + c] = dc; }
+        a[c] = lc;
+      }
+      if (lane < 8) {  // unit lower L_jj into the chunk layout (rows 0..7 of chunks 2j, 2j+1)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          double v[4];
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const int c = 4 * h + qq;
+            v[qq] = c < lr ? a[c] : (c == lr ? 1.0 : 0.0);
+          }
+          double* dst = Lch + L::chunk_off(2 * j + h) + lr * 4;
+          *reinterpret_cast<double2*>(dst) = make_double2(v[0], v[1]);
+          *reinterpret_cast<double2*>(dst + 2) = make_double2(v[2], v[3]);
+        }
+      }
+      if (!ok && lane == 0) *failflag = 1;
+    }
+    __syncthreads();
+    // ---- P3: triangular solve, one thread per row below the block; the last thread carries the right-hand side ----
+    double l[8];
+    const bool is_row = tid >= 8 * (j + 1) && tid < P;
+    const bool is_rhs = tid == L::THREADS - 1;
+    if (is_row || is_rhs) {
+      double a[8], u[8];
+      if (is_row) {
+#pragma unroll
+        for (int c = 0; c < 8; c += 2) {
+          const double2 v = *reinterpret_cast<const double2*>(praw + tid * PLD + c);
+          a[c] = v.x; a[c + 1] = v.y;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) a[c] = dj[16 + c];
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        double v = a[c];
+#pragma unroll
+        for (int k2 = 0; k2 < c; ++k2) v = fma(-u[k2], Lch[L::chunk_off(2 * j + k2 / 4) + c * 4 + (k2 & 3)], v);
+        u[c] = v;
+        l[c] = v * dj[8 + c];
+      }
+      if (is_row) {
+        double* d0 = Lch + L::chunk_off(2 * j) + (tid - 8 * j) * 4;
+        double* d1 = Lch + L::chunk_off(2 * j + 1) + (tid - 8 * j) * 4;
+        *reinterpret_cast<double2*>(d0) = make_double2(l[0], l[1]);
+        *reinterpret_cast<double2*>(d0 + 2) = make_double2(l[2], l[3]);
+        *reinterpret_cast<double2*>(d1) = make_double2(l[4], l[5]);
+        *reinterpret_cast<double2*>(d1 + 2) = make_double2(l[6], l[7]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) { sm[L::O_WP + 8 * j + c] = l[c]; dj[24 + c] = u[c]; }
+      }
+    }
+    __syncthreads();
+    // ---- P4: trailing update C(I,J') -= L(I,j) D_j L(J',j)' with DMMA; right-hand side rows below ----
+    if (j < NT - 1) {
+      const double nd0 = -dj[q], nd1 = -dj[4 + q];
+      const double* __restrict__ ch0 = Lch + L::chunk_off(2 * j) + r * 4 + q;
+      const double* __restrict__ ch1 = Lch + L::chunk_off(2 * j + 1) + r * 4 + q;
+#pragma unroll
+      for (int I = j + 1; I < NT; ++I) {
+        if (L::rowwarp(I) != warp) continue;
+        const double a0raw = ch0[32 * (I - j)], a1raw = ch1[32 * (I - j)];
+        const double a0 = a0raw * nd0, a1 = a1raw * nd1;
+#pragma unroll
+        for (int J2 = j + 1; J2 <= I; ++J2) {
+          const int slot = L::slotbase(I) + J2;
+          const double b0 = (J2 == I) ? a0raw : ch0[32 * (J2 - j)];
+          const double b1 = (J2 == I) ? a1raw : ch1[32 * (J2 - j)];
+          dmma884(acc[slot][0], acc[slot][1], a0, b0);
+          dmma884(acc[slot][0], acc[slot][1], a1, b1);
+        }
+      }
+      if (is_row) {
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int c = 0; c < 8; c += 2) { s0 = fma(l[c], dj[24 + c], s0); s1 = fma(l[c + 1], dj[25 + c], s1); }
+        racc -= s0 + s1;
+      }
+    }
+  }
+  // ---- back substitution L' sol = w' (w' = D^-1 L^-1 rhs from the fused forward pass) ----
+  double bacc = tid < P ? sm[L::O_WP + tid] : 0.0;
+  const int mych = L::chunk_off(tid >> 2) + (tid & 3) - 32 * (tid >> 3);  // + 4*row gives L[row][tid]
+#pragma unroll
+  for (int J = NT - 1; J >= 0; --J) {
+    if (warp == (8 * J) / 32) {
+      const int base = (8 * J) % 32, c = lane - base;
+      const bool mine = c >= 0 && c < 8;
+#pragma unroll
+      for (int cc = 7; cc >= 1; --cc) {
+        const double xv = __shfl_sync(0xffffffffu, bacc, base + cc);
+        if (mine && c < cc) bacc = fma(-Lch[L::chunk_off(2 * J + (c >> 2)) + cc * 4 + (c & 3)], xv, bacc);
+      }
+      if (mine) sm[L::O_SOL + 8 * J + c] = bacc;
+    }
+    __syncthreads();
+    if (tid < 8 * J) {
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int rr = 0; rr < 8; rr += 2) {
+        s0 = fma(Lch[mych + 4 * (8 * J + rr)], sm[L::O_SOL + 8 * J + rr], s0);
+        s1 = fma(Lch[mych + 4 * (8 * J + rr + 1)], sm[L::O_SOL + 8 * J + rr + 1], s1);
+      }
+      bacc -= s0 + s1;
+    }
+  }
+  __syncthreads();
+  return *failflag == 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// The solve kernel: persistent CTAs, one problem per CTA at a time.
+// ---------------------------------------------------------------------------------------------------------
+template <int N, int K, int W, int MINB>
+__global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
+  using L = DmLayout<N, K, W>;
+  static_assert(L::P < L::THREADS, "the last thread carries the right-hand side");
+  constexpr int P = L::P, M = L::M, THREADS = L::THREADS, MAXS = L::maxslots(), STRIDE = N + 2 * M + K;
+  extern __shared__ __align__(16) double sm[];
+  const int tid = threadIdx.x;
+  double* const X = sm + L::O_X;
+  double* const Y = sm + L::O_Y;
+  double* const S = sm + L::O_S;
+  double* const Z = sm + L::O_Z;
+  double* const IB = sm + L::O_IB;
+  double* const T1 = sm + L::O_T1;
+  double* const T2 = sm + L::O_T2;
+  double* const RPE = sm + L::O_RPE;
+  double* const SOL = sm + L::O_SOL;
+  double* const RED = sm + L::O_RED;
+  const double* const region = sm + L::O_REGION;
+  const double tol2 = a.kkt_tol * a.kkt_tol, tau = 0.995;  // qp.cc:192
+
+  for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
+    const double* __restrict__ Gp = a.G + prob * (N * N);
+    const double* __restrict__ Ap = K > 0 ? a.A + prob * (N * K) : nullptr;
+    double* __restrict__ vp = a.vars + prob * STRIDE;
+    __syncthreads();  // previous problem fully retired
+    dm_stage_issue<N, K, W>(sm + L::O_REGION, Gp, Ap);
+    for (int i = tid; i < N; i += THREADS) { sm[L::O_C + i] = a.c[prob * N + i]; X[i] = 0.0; }
+    for (int i = tid; i < K; i += THREADS) { sm[L::O_B + i] = a.b[prob * K + i]; Y[i] = 0.0; }
+    for (int i = tid; i < M; i += THREADS) IB[i] = a.ib[prob * M + i];
+    double acc[MAXS][2];
+    int status = -1, iters = 0;
+    // ---- ComputeInitialGuess (qp.cc:439-482) ----
+    if (a.guess == MO_GUESS_USER_PROVIDED) {
+      for (int i = tid; i < N; i += THREADS) X[i] = vp[i];
+      for (int i = tid; i < M; i += THREADS) { S[i] = vp[N + i]; Z[i] = vp[N + M + K + i]; }
+      for (int i = tid; i < K; i += THREADS) Y[i] = vp[N + M + i];
+    } else {
+      if (a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED) {
+        cp_async_wait_all();
+        __syncthreads();
+        dm_assemble<N, K, W, MAXS>(acc, sm, false);
+        const double rhs = tid < N ? -sm[L::O_C + tid] : (tid < P ? -sm[L::O_B + tid - N] : 0.0);
+        const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm);
+        if (!ok) status = MO_QP_FAILED_FACTORIZATION;
+        dm_stage_issue<N, K, W>(sm + L::O_REGION, Gp, Ap);  // L overwrote the staged G
+        if (tid < N) X[tid] = ok ? SOL[tid] : 0.0;
+        else if (tid < P) Y[tid - N] = ok ? -SOL[tid] : 0.0;
+      }
+      __syncthreads();
+      if (tid < N) {  // clamp in list order (ClampX, qp.hpp:43-53), s = max(1e-9, a x + b), z = 1/s (qp.cc:462-481)
+        double xv = X[tid];
+        const double b0 = IB[2 * tid], b1 = IB[2 * tid + 1];
+        xv = xv > -b0 ? xv : -b0;
+        xv = xv < b1 ? xv : b1;
+        const double s0 = fmax(1.0e-9, xv + b0), s1 = fmax(1.0e-9, b1 - xv);
+        X[tid] = xv;
+        S[2 * tid] = s0; S[2 * tid + 1] = s1;
+        Z[2 * tid] = 1.0 / s0; Z[2 * tid + 1] = 1.0 / s1;
+      }
+    }
+    double mu = a.initial_mu, alpha_p = 1.0, alpha_d = 1.0;
+    double kkt[4] = {0.0, 0.0, 0.0, 0.0};
+    bool first = true;
+    // ---- Solve loop (qp.cc:110-149); each trip = residuals of the current state, bookkeeping, one Newton step ----
+    while (status < 0) {
+      cp_async_wait_all();
+      __syncthreads();
+      // (1) EvaluateKKTConditions (qp.cc:391-420): symmetric matvec from the staged lower trapezoid
+      for (int task = tid; task < 2 * N + K; task += THREADS) {
+        if (task < N) {  // row pass: c_i + sum_{j <= i} G(i,j) x_j
+          const int i = task;
+          double s0 = sm[L::O_C + i], s1 = 0.0;
+          for (int jb = 0; 8 * jb <= i; ++jb) {
+            const int len = N - 8 * jb + 2;
+            const double* col = region + 8 * (jb * (N + 2) - 4 * jb * (jb - 1)) + i - 8 * jb;
+            const int cnt = i - 8 * jb + 1 < 8 ? i - 8 * jb + 1 : 8;
+#pragma unroll
+            for (int jj = 0; jj < 8; jj += 2) {
+              if (jj < cnt) s0 = fma(col[jj * len], X[8 * jb + jj], s0);
+              if (jj + 1 < cnt) s1 = fma(col[(jj + 1) * len], X[8 * jb + jj + 1], s1);
+            }
+          }
+          T1[i] = s0 + s1;
+        } else if (task < 2 * N) {  // column pass: sum_{i > j} G(i,j) x_i  -  (A' y)_j
+          const int j = task - N;
+          const double* col = region + L::gcol_off(j) - 8 * (j / 8);
+          double s0 = 0.0, s1 = 0.0;
+          int i = j + 1;
+          if ((i & 1) && i < N) { s0 = fma(col[i], X[i], s0); ++i; }
+          for (; i + 1 < N; i += 2) { s0 = fma(col[i], X[i], s0); s1 = fma(col[i + 1], X[i + 1], s1); }
+          if (i < N) s0 = fma(col[i], X[i], s0);
+          if (K > 0) {
+            const double* acol = region + L::GSIZE + j * L::ALD;
+            double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+            for (int r2 = 0; r2 < K; r2 += 2) { t0 = fma(acol[r2], Y[r2], t0); t1 = fma(acol[r2 + 1], Y[r2 + 1], t1); }
+            s0 -= t0; s1 -= t1;
+          }
+          T2[j] = s0 + s1;
+        } else {  // r_pe = A x + b
+          const int r2 = task - 2 * N;
+          const double* arow = region + L::GSIZE + r2;
+          double s0 = sm[L::O_B + r2], s1 = 0.0;
+#pragma unroll 8
+          for (int j = 0; j < N; j += 2) { s0 = fma(arow[j * L::ALD], X[j], s0); s1 = fma(arow[(j + 1) * L::ALD], X[j + 1], s1); }
+          RPE[r2] = s0 + s1;
+        }
+      }
+      __syncthreads();
+      // (2) per-variable residuals, Sigma, r_aug pieces; norms (ComputeErrors, qp.cc:423-437)
+      double red[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // |r_d|^2, |r_pe|^2, |r_pi|^2, sum (sz)^2, sum sz, #(s <= 0)
+      if (tid < N) {
+        const int v = tid;
+        const double base = T1[v] + T2[v];
+        const double s0 = S[2 * v], s1 = S[2 * v + 1], z0 = Z[2 * v], z1 = Z[2 * v + 1], xv = X[v];
+        const double p0 = (xv + IB[2 * v]) - s0, p1 = (IB[2 * v + 1] - xv) - s1;
+        const double i0 = fast_rcp(s0), i1 = fast_rcp(s1);
+        const double w0 = z0 * i0, w1 = z1 * i1;
+        sm[L::O_SIG + v] = w0 + w1;
+        const double rdv = (base - z0) + z1;
+        const double c0 = s0 * z0, c1 = s1 * z1;
+        red[0] = rdv * rdv;
+        red[2] = fma(p0, p0, p1 * p1);
+        red[3] = fma(c0, c0, c1 * c1);
+        red[4] = c0 + c1;
+        red[5] = ((s0 > 0.0) ? 0.0 : 1.0) + ((s1 > 0.0) ? 0.0 : 1.0);
+        T1[v] = base + fma(w0, p0, -(w1 * p1));  // r_aug without the mu term (qp.cc:337-342)
+        T2[v] = i0 - i1;
+      } else if (tid < P) {
+        const double pe = RPE[tid - N];
+        red[1] = pe * pe;
+      }
+      block_reduce<W, 6, false>(red, RED);
+      // (3) bookkeeping of the Solve loop: errors of the step just taken, termination, barrier update
+      const double mu_c = red[4] / (double)M;  // ComputeMu, qp.cc:509-516
+      const double corrected = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
+      const double comp2 = corrected > 0.0 ? corrected : 0.0;
+      if (first) {
+        first = false;
+        mu = a.init_mu_with_comp ? mu_c : a.initial_mu;
+      } else {
+        const double max2 = fmax(fmax(red[0], comp2), fmax(red[1], red[2]));
+        kkt[0] = sqrt(red[0]); kkt[1] = sqrt(comp2); kkt[2] = sqrt(red[1]); kkt[3] = sqrt(red[2]);
+        if (a.iter_log && tid == 0) {
+          double* row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+          row[4] = kkt[0]; row[5] = kkt[1]; row[6] = kkt[2]; row[7] = kkt[3];
+          row[8] = mu; row[9] = alpha_p; row[10] = alpha_d; row[11] = qnan(); row[12] = qnan(); row[13] = qnan();
+        }
+        ++iters;
+        if (max2 < tol2 && mu_c < a.comp_tol) status = MO_QP_SATISFIED_KKT_TOL;  // qp.cc:132-137
+        else if (iters >= a.max_iterations) status = MO_QP_MAX_ITERATIONS;
+        else if (max2 <= mu * mu || !a.decrease_mu_only_on_small_error)          // qp.cc:140-146
+          mu = (a.strategy == MO_BARRIER_FIXED_DECREASE) ? mu * a.sigma : a.sigma * mu_c;
+      }
+      if (status < 0 && red[5] != 0.0) status = MO_QP_NONPOSITIVE_SLACK;  // F_ASSERT(all s > 0), qp.cc:285
+      if (status >= 0) break;
+      if (a.iter_log && tid == 0) {  // kkt_initial of the coming iteration (ComputeErrors with the new mu, qp.cc:118)
+        double* row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+        const double cr = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
+        row[0] = sqrt(red[0]); row[1] = sqrt(cr > 0.0 ? cr : 0.0); row[2] = sqrt(red[1]); row[3] = sqrt(red[2]);
+      }
+      // (4) ComputeLDLT + SolveForUpdate: rhs = -[r_aug; r_pe]  ->  SOL = [dx; -dy]
+      const double rhs = tid < N ? -fma(-mu, T2[tid], T1[tid]) : (tid < P ? -RPE[tid - N] : 0.0);
+      dm_assemble<N, K, W, MAXS>(acc, sm, true);
+      const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm);
+      if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
+      dm_stage_issue<N, K, W>(sm + L::O_REGION, Gp, Ap);  // next trip's G, A: overlaps the update below
+      // (5) ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199)
+      double al[2] = {1.0, 1.0};
+      double d0 = 0.0, d1 = 0.0, e0 = 0.0, e1 = 0.0;
+      if (tid < N) {
+        const int v = tid;
+        const double s0 = S[2 * v], s1 = S[2 * v + 1], z0 = Z[2 * v], z1 = Z[2 * v + 1], xv = X[v], dxv = SOL[v];
+        const double p0 = (xv + IB[2 * v]) - s0, p1 = (IB[2 * v + 1] - xv) - s1;
+        const double i0 = fast_rcp(s0), i1 = fast_rcp(s1);
+        d0 = dxv + p0; d1 = p1 - dxv;
+        e0 = fma(mu, i0, -fma(z0 * i0, d0, z0));
+        e1 = fma(mu, i1, -fma(z1 * i1, d1, z1));
+        if (s0 + d0 <= 0.0 && fabs(d0) > 0) al[0] = fmin(al[0], -tau * s0 / d0);
+        if (s1 + d1 <= 0.0 && fabs(d1) > 0) al[0] = fmin(al[0], -tau * s1 / d1);
+        if (z0 + e0 <= 0.0 && fabs(e0) > 0) al[1] = fmin(al[1], -tau * z0 / e0);
+        if (z1 + e1 <= 0.0 && fabs(e1) > 0) al[1] = fmin(al[1], -tau * z1 / e1);
+      }
+      block_reduce<W, 2, true>(al, RED);
+      alpha_p = al[0]; alpha_d = al[1];
+      if (tid < N) {
+        const int v = tid;
+        X[v] = fma(SOL[v], alpha_p, X[v]);
+        S[2 * v] = fma(d0, alpha_p, S[2 * v]); S[2 * v + 1] = fma(d1, alpha_p, S[2 * v + 1]);
+        Z[2 * v] = fma(e0, alpha_d, Z[2 * v]); Z[2 * v + 1] = fma(e1, alpha_d, Z[2 * v + 1]);
+      } else if (tid < P) {
+        Y[tid - N] = fma(-SOL[tid], alpha_d, Y[tid - N]);
+      }
+    }
+    // ---- results ----
+    cp_async_wait_all();
+    __syncthreads();
+    for (int i = tid; i < N; i += THREADS) vp[i] = X[i];
+    for (int i = tid; i < M; i += THREADS) { vp[N + i] = S[i]; vp[N + M + K + i] = Z[i]; }
+    for (int i = tid; i < K; i += THREADS) vp[N + M + i] = Y[i];
+    if (tid == 0) {
+      a.status[prob] = status;
+      a.iters[prob] = iters;
+      if (a.kkt_final) {
+        double* kf = a.kkt_final + prob * 4;
+        kf[0] = kkt[0]; kf[1] = kkt[1]; kf[2] = kkt[2]; kf[3] = kkt[3];
+      }
+      if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
+        double mn = qnan(), li = qnan();
+        if (K > 0) {
+          mn = Y[0]; li = fabs(Y[0]);
+          for (int r2 = 1; r2 < K; ++r2) { mn = fmin(mn, Y[r2]); li = fmax(li, fabs(Y[r2])); }
+        }
+        a.lagrange[prob * 2] = mn;
+        a.lagrange[prob * 2 + 1] = li;
+      }
+    }
+  }
+}
+
+}  // namespace mo

@@ -149,7 +149,7 @@ def test_box_synth_vs_reference_golden(dev, golden_box, n, gname, guess, explici
             assert_log_close(out.iter_log[p, :its], g[f"{tag}_log"][p, :its])
 
 
-@pytest.mark.parametrize("n,k,B", [(8, 2, 20000), (8, 0, 5000), (4, 1, 5000), (6, 2, 2000), (12, 3, 2000), (32, 8, 300), (64, 16, 40)])
+@pytest.mark.parametrize("n,k,B", [(8, 2, 20000), (8, 0, 5000), (4, 1, 5000), (6, 2, 2000), (12, 3, 2000), (16, 8, 1500), (32, 8, 1500), (64, 16, 400)])
 @pytest.mark.parametrize("guess", [abi.MO_GUESS_NAIVE, abi.MO_GUESS_SOLVE_EQUALITY_CONSTRAINED])
 def test_box_synth_vs_oracle(dev, oracle, n, k, B, guess):
     """Fresh seeded batches: CUDA path vs the oracle on identical bytes."""
