@@ -170,7 +170,11 @@ bool tpp_eligible(int n, int k, int m, int flags, bool ragged, int strategy) {
 }
 
 // (N, K, warps per CTA, min CTAs per SM) shapes with a DMMA CTA-per-problem instantiation (box pairs, m == 2n).
-#define MO_DM_SHAPES(X) X(64, 16, 4, 5) X(32, 8, 2, 8) X(16, 8, 1, 16)
+#ifndef MO_DM64_W
+#define MO_DM64_W 4     /* measured on B200, 64K QPs n=64: W=4/MINB=4 35.7 ms, W=4/MINB=5 41.9, W=8/MINB=4 61.7 */
+#define MO_DM64_MINB 4
+#endif
+#define MO_DM_SHAPES(X) X(64, 16, MO_DM64_W, MO_DM64_MINB) X(32, 8, 2, 8) X(16, 8, 1, 16)
 
 template <int N, int K, int W, int MINB>
 int launch_dm(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
@@ -653,3 +657,15 @@ int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_
 }
 
 }  // extern "C"
+
+#ifdef MO_DM_TRACE
+extern "C" int mo_debug_read_trace(long long* out, int cap) {
+  int n = 0;
+  cudaMemcpyFromSymbol(&n, mo::g_dm_trace_n, sizeof(int));
+  if (n > cap) n = cap;
+  cudaMemcpyFromSymbol(out, mo::g_dm_trace, sizeof(long long) * n);
+  int zero = 0;
+  cudaMemcpyToSymbol(mo::g_dm_trace_n, &zero, sizeof(int));
+  return n;
+}
+#endif

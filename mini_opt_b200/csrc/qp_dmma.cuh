@@ -69,8 +69,8 @@ struct DmLayout {
   // shared memory map (doubles)
   static constexpr int O_REGION = 0;
   static constexpr int O_PRAW = O_REGION + REGION;
-  static constexpr int O_DJ = O_PRAW + P * PLD;       // d[8], dinv[8], rhs exchange [8], w (unscaled) [8]
-  static constexpr int O_X = O_DJ + 32;
+  static constexpr int O_DJ = O_PRAW + P * PLD;       // 2 x {d[8], 1/d[8]}, rhs exchange [8], w (unscaled) [8]
+  static constexpr int O_X = O_DJ + 48;
   static constexpr int O_Y = O_X + N;
   static constexpr int O_S = O_Y + (K > 0 ? K : 2);
   static constexpr int O_Z = O_S + M;
@@ -89,6 +89,21 @@ struct DmLayout {
   static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
 };
 
+#ifdef MO_DM_TRACE
+// Debug build only: thread 0 of CTA 0 stamps phase boundaries into a shared-memory ring (cheap), dumped at kernel end.
+__device__ long long g_dm_trace[2048];
+__device__ int g_dm_trace_n;
+__shared__ long long s_dm_trace[1024];
+__shared__ int s_dm_trace_n;
+#define DM_T(tag) do { if (blockIdx.x == 0 && threadIdx.x == 0 && s_dm_trace_n < 1024) { s_dm_trace[s_dm_trace_n++] = (clock64() << 8) | (tag); } } while (0)
+#define DM_T_INIT() do { if (threadIdx.x == 0) s_dm_trace_n = 0; __syncthreads(); } while (0)
+#define DM_T_DUMP() do { __syncthreads(); if (blockIdx.x == 0 && threadIdx.x == 0) { for (int i_ = 0; i_ < s_dm_trace_n; ++i_) g_dm_trace[i_] = s_dm_trace[i_]; g_dm_trace_n = s_dm_trace_n; } } while (0)
+#else
+#define DM_T(tag) do {} while (0)
+#define DM_T_INIT() do {} while (0)
+#define DM_T_DUMP() do {} while (0)
+#endif
+
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
       : "+d"(c0), "+d"(c1)
@@ -102,16 +117,14 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// Reciprocal with a 3-deep dependent chain: x(1 + e + e^2), e = 1 - d x  (|e| ~ 2^-23 after MUFU.RCP64H + one step
-// folded in): full double accuracy for normal d.
+// Reciprocal with a 3-deep dependent FMA chain after MUFU.RCP64H: x(1 + e + e^2), e = 1 - d x, |e| < 2^-20, so the
+// truncation error e^3 < 2^-60 is below double rounding; used on the pivot chain of the diagonal block.
 __device__ __forceinline__ double rcp_chain(double d) {
   double x;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
   const double e = fma(-d, x, 1.0);
   const double p = fma(e, e, e);
-  x = fma(x, p, x);
-  const double e2 = fma(-d, x, 1.0);
-  return fma(x, e2, x);
+  return fma(x, p, x);
 }
 
 // Sum / min over the CTA of NV values per thread; result broadcast to every thread. `red` holds NV*W doubles.
@@ -195,10 +208,73 @@ __device__ __forceinline__ void dm_assemble(double (&acc)[MAXS][2], const double
   }
 }
 
+// LDL' of the 8x8 diagonal block of panel j (raw values in praw rows 8j..8j+7): lane = row, pivots taken in PAIRS so
+// that the two reciprocals of a pair overlap (1/d1 = a00 / det): 4 dependent reciprocal latencies per block, not 8.
+// Writes d, 1/d into djb[0..15], the pivots into DALL and the unit lower L_jj into chunks (offA, offB) rows 0..7.
+template <int N, int K, int W>
+__device__ __forceinline__ void dm_diag_block(double* __restrict__ sm, int j, double* __restrict__ djb, int offA, int offB) {
+  using L = DmLayout<N, K, W>;
+  const int lane = threadIdx.x & 31, lr = lane & 7;
+  const double* __restrict__ praw = sm + L::O_PRAW;
+  double* __restrict__ Lch = sm + L::O_REGION;
+  double a[8];
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    const double2 v = *reinterpret_cast<const double2*>(praw + (8 * j + lr) * L::PLD + c);
+    a[c] = v.x; a[c + 1] = v.y;
+  }
+  bool ok = true;
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    const double a00 = __shfl_sync(0xffffffffu, a[c], c);
+    const double a10 = __shfl_sync(0xffffffffu, a[c], c + 1);
+    const double a11 = __shfl_sync(0xffffffffu, a[c + 1], c + 1);
+    const double det = fma(a00, a11, -(a10 * a10));
+    const double inv0 = rcp_chain(a00), rdet = rcp_chain(det);
+    const double inv1 = a00 * rdet;               // 1 / d1 with d1 = det / a00
+    const double d1 = fma(-(a10 * inv0), a10, a11);
+    ok = ok && (fabs(a00) > 0.0) && (fabs(a00) <= 1.7976931348623157e308) && (fabs(d1) > 0.0) &&
+         (fabs(d1) <= 1.7976931348623157e308);
+    const double u0 = a[c], l0 = u0 * inv0;
+    const double u1 = fma(-l0, a10, a[c + 1]), l1 = u1 * inv1;
+#pragma unroll
+    for (int c2 = c + 2; c2 < 8; ++c2) {
+      const double v0 = __shfl_sync(0xffffffffu, u0, c2), v1 = __shfl_sync(0xffffffffu, u1, c2);
+      a[c2] = fma(-l1, v1, fma(-l0, v0, a[c2]));
+    }
+    if (lane == c) {
+      djb[c] = a00; djb[8 + c] = inv0; djb[c + 1] = d1; djb[9 + c] = inv1;
+      sm[L::O_DALL + 8 * j + c] = a00; sm[L::O_DALL + 8 * j + c + 1] = d1;
+    }
+    a[c] = l0; a[c + 1] = l1;
+  }
+  if (lane < 8) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      double v[4];
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) {
+        const int c = 4 * h + qq;
+        v[qq] = c < lr ? a[c] : (c == lr ? 1.0 : 0.0);
+      }
+      double* dst = Lch + (h ? offB : offA) + lr * 4;
+      *reinterpret_cast<double2*>(dst) = make_double2(v[0], v[1]);
+      *reinterpret_cast<double2*>(dst + 2) = make_double2(v[2], v[3]);
+    }
+  }
+  if (!ok && lane == 0) *reinterpret_cast<int*>(sm + L::O_RED + 8 * W) = 1;
+}
+
 // Unpivoted LDL' of the matrix held in `acc` (right-looking, 8-column panels, DMMA trailing updates) fused with the
 // forward substitution of the right-hand side `racc` (thread t < P holds entry t), then the back substitution.
 // On return sm[O_SOL .. O_SOL+P) = K^-1 rhs for every thread to read. Returns false (uniformly) on a zero or
 // non-finite pivot (-> MO_QP_FAILED_FACTORIZATION, the batched stand-in for the exception of qp.cc:303-307).
+//
+// Schedule per panel j (two CTA barriers): [P3: one thread per row below the block solves against L_jj D_j]  |barrier|
+// [P4: every warp first updates and spills its tiles of column j+1; the owner of tile row j+1 then factors the NEXT
+// diagonal block (look-ahead) while the other warps finish the trailing update]  |barrier|. The panel loop is a RUNTIME
+// loop (tile loops stay unrolled so that the accumulators keep static register names): fully unrolled it is 0.5 MB of
+// SASS. j = -1 is the prologue (spill column 0, factor block 0).
 template <int N, int K, int W, int MAXS>
 __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double racc, double* __restrict__ sm) {
   using L = DmLayout<N, K, W>;
@@ -206,140 +282,137 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = lane >> 2, q = lane & 3;
   double* __restrict__ Lch = sm + L::O_REGION;
   double* __restrict__ praw = sm + L::O_PRAW;
-  double* __restrict__ dj = sm + L::O_DJ;
+  double* __restrict__ dj = sm + L::O_DJ;  // [0..31] d, 1/d of the panel (double buffered), [32..39] rhs block, [40..47] w
   int* failflag = reinterpret_cast<int*>(sm + L::O_RED + 8 * W);
   if (tid == 0) *failflag = 0;
-#pragma unroll
-  for (int j = 0; j < NT; ++j) {
-    // ---- P1: spill panel column j (raw values) and the right-hand side entries of block j ----
-#pragma unroll
-    for (int I = j; I < NT; ++I) {
-      if (L::rowwarp(I) != warp) continue;
-      const int slot = L::slotbase(I) + j;
-      *reinterpret_cast<double2*>(praw + (8 * I + r) * PLD + 2 * q) = make_double2(acc[slot][0], acc[slot][1]);
-    }
-    if (tid >= 8 * j && tid < 8 * j + 8) dj[16 + tid - 8 * j] = racc;
-    __syncthreads();
-    // ---- P2: LDL' of the 8x8 diagonal block: lane = row, column by column, shuffles ----
-    if (warp == j % W) {
-      const int lr = lane & 7;
-      double a[8];
-#pragma unroll
-      for (int c = 0; c < 8; c += 2) {
-        const double2 v = *reinterpret_cast<const double2*>(praw + (8 * j + lr) * PLD + c);
-        a[c] = v.x; a[c + 1] = v.y;
-      }
-      bool ok = true;
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const double dc = __shfl_sync(0xffffffffu, a[c], c);
-        ok = ok && (fabs(dc) > 0.0) && (fabs(dc) <= 1.7976931348623157e308);
-        const double inv = rcp_chain(dc);
-        const double uc = a[c];
-        const double lc = uc * inv;
-#pragma unroll
-        for (int c2 = c + 1; c2 < 8; ++c2) {
-          const double v = __shfl_sync(0xffffffffu, uc, c2);
-          a[c2] = fma(-lc, v, a[c2]);
-        }
-        if (lane == c) { dj[c] = dc; dj[8 + c] = inv; sm[L::O_DALL + 8 * j + c] = dc; }
-        a[c] = lc;
-      }
-      if (lane < 8) {  // unit lower L_jj into the chunk layout (rows 0..7 of chunks 2j, 2j+1)
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          double v[4];
-#pragma unroll
-          for (int qq = 0; qq < 4; ++qq) {
-            const int c = 4 * h + qq;
-            v[qq] = c < lr ? a[c] : (c == lr ? 1.0 : 0.0);
-          }
-          double* dst = Lch + L::chunk_off(2 * j + h) + lr * 4;
-          *reinterpret_cast<double2*>(dst) = make_double2(v[0], v[1]);
-          *reinterpret_cast<double2*>(dst + 2) = make_double2(v[2], v[3]);
-        }
-      }
-      if (!ok && lane == 0) *failflag = 1;
-    }
-    __syncthreads();
-    // ---- P3: triangular solve, one thread per row below the block; the last thread carries the right-hand side ----
-    double l[8];
+  double l[8];
+#pragma unroll 1
+  for (int j = -1; j < NT; ++j) {
+    const int off0 = j >= 0 ? L::chunk_off(2 * j) : 0, off1 = off0 + (P - 8 * j) * 4 + 4;
+    const double* __restrict__ djc = dj + (j & 1) * 16;
     const bool is_row = tid >= 8 * (j + 1) && tid < P;
-    const bool is_rhs = tid == L::THREADS - 1;
-    if (is_row || is_rhs) {
-      double a[8], u[8];
-      if (is_row) {
+    if (j >= 0) {
+      // ---- P3: triangular solve, one thread per row below the block; the last thread carries the right-hand side ----
+      const bool is_rhs = tid == L::THREADS - 1;
+      if (is_row || is_rhs) {
+        double a[8], u[8];
+        if (is_row) {
 #pragma unroll
-        for (int c = 0; c < 8; c += 2) {
-          const double2 v = *reinterpret_cast<const double2*>(praw + tid * PLD + c);
-          a[c] = v.x; a[c + 1] = v.y;
+          for (int c = 0; c < 8; c += 2) {
+            const double2 v = *reinterpret_cast<const double2*>(praw + tid * PLD + c);
+            a[c] = v.x; a[c + 1] = v.y;
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) a[c] = dj[32 + c];
         }
-      } else {
 #pragma unroll
-        for (int c = 0; c < 8; ++c) a[c] = dj[16 + c];
+        for (int c = 0; c < 8; ++c) {
+          double v = a[c];
+#pragma unroll
+          for (int k2 = 0; k2 < c; ++k2) v = fma(-u[k2], Lch[(k2 < 4 ? off0 : off1) + c * 4 + (k2 & 3)], v);
+          u[c] = v;
+          l[c] = v * djc[8 + c];
+        }
+        if (is_row) {
+          double* d0 = Lch + off0 + (tid - 8 * j) * 4;
+          double* d1 = Lch + off1 + (tid - 8 * j) * 4;
+          *reinterpret_cast<double2*>(d0) = make_double2(l[0], l[1]);
+          *reinterpret_cast<double2*>(d0 + 2) = make_double2(l[2], l[3]);
+          *reinterpret_cast<double2*>(d1) = make_double2(l[4], l[5]);
+          *reinterpret_cast<double2*>(d1 + 2) = make_double2(l[6], l[7]);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) { sm[L::O_WP + 8 * j + c] = l[c]; dj[40 + c] = u[c]; }
+        }
       }
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        double v = a[c];
-#pragma unroll
-        for (int k2 = 0; k2 < c; ++k2) v = fma(-u[k2], Lch[L::chunk_off(2 * j + k2 / 4) + c * 4 + (k2 & 3)], v);
-        u[c] = v;
-        l[c] = v * dj[8 + c];
-      }
-      if (is_row) {
-        double* d0 = Lch + L::chunk_off(2 * j) + (tid - 8 * j) * 4;
-        double* d1 = Lch + L::chunk_off(2 * j + 1) + (tid - 8 * j) * 4;
-        *reinterpret_cast<double2*>(d0) = make_double2(l[0], l[1]);
-        *reinterpret_cast<double2*>(d0 + 2) = make_double2(l[2], l[3]);
-        *reinterpret_cast<double2*>(d1) = make_double2(l[4], l[5]);
-        *reinterpret_cast<double2*>(d1 + 2) = make_double2(l[6], l[7]);
-      } else {
-#pragma unroll
-        for (int c = 0; c < 8; ++c) { sm[L::O_WP + 8 * j + c] = l[c]; dj[24 + c] = u[c]; }
-      }
+      DM_T(3);
+      __syncthreads();
+      DM_T(4);
+      if (j == NT - 1) break;
     }
-    __syncthreads();
-    // ---- P4: trailing update C(I,J') -= L(I,j) D_j L(J',j)' with DMMA; right-hand side rows below ----
-    if (j < NT - 1) {
-      const double nd0 = -dj[q], nd1 = -dj[4 + q];
-      const double* __restrict__ ch0 = Lch + L::chunk_off(2 * j) + r * 4 + q;
-      const double* __restrict__ ch1 = Lch + L::chunk_off(2 * j + 1) + r * 4 + q;
-#pragma unroll
-      for (int I = j + 1; I < NT; ++I) {
-        if (L::rowwarp(I) != warp) continue;
-        const double a0raw = ch0[32 * (I - j)], a1raw = ch1[32 * (I - j)];
-        const double a0 = a0raw * nd0, a1 = a1raw * nd1;
-#pragma unroll
-        for (int J2 = j + 1; J2 <= I; ++J2) {
-          const int slot = L::slotbase(I) + J2;
-          const double b0 = (J2 == I) ? a0raw : ch0[32 * (J2 - j)];
-          const double b1 = (J2 == I) ? a1raw : ch1[32 * (J2 - j)];
-          dmma884(acc[slot][0], acc[slot][1], a0, b0);
-          dmma884(acc[slot][0], acc[slot][1], a1, b1);
-        }
-      }
-      if (is_row) {
+    // ---- P4: trailing update C(I,J') -= L(I,j) D_j L(J',j)' with DMMA; column j+1 first, then look-ahead ----
+    double nd0 = 0.0, nd1 = 0.0, bn0 = 0.0, bn1 = 0.0;
+    const double* __restrict__ ch0 = Lch + off0 + r * 4 + q - 32 * j;  // + 32*I -> row 8I + r of chunk 2j
+    const double* __restrict__ ch1 = Lch + off1 + r * 4 + q - 32 * j;
+    if (j >= 0) {
+      nd0 = -djc[q]; nd1 = -djc[4 + q];
+      if (j + 1 < NT) { bn0 = ch0[32 * (j + 1)]; bn1 = ch1[32 * (j + 1)]; }  // B fragments of tile column j+1
+      if (is_row) {  // forward substitution of the right-hand side rows below the block
         double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-        for (int c = 0; c < 8; c += 2) { s0 = fma(l[c], dj[24 + c], s0); s1 = fma(l[c + 1], dj[25 + c], s1); }
+        for (int c = 0; c < 8; c += 2) { s0 = fma(l[c], dj[40 + c], s0); s1 = fma(l[c + 1], dj[41 + c], s1); }
         racc -= s0 + s1;
       }
     }
-  }
-  // ---- back substitution L' sol = w' (w' = D^-1 L^-1 rhs from the fused forward pass) ----
-  double bacc = tid < P ? sm[L::O_WP + tid] : 0.0;
-  const int mych = L::chunk_off(tid >> 2) + (tid & 3) - 32 * (tid >> 3);  // + 4*row gives L[row][tid]
+    if (tid >= 8 * (j + 1) && tid < 8 * (j + 1) + 8) dj[32 + tid - 8 * (j + 1)] = racc;
 #pragma unroll
+    for (int I = 0; I < NT; ++I) {  // pass A: tiles of column j+1 -> update, spill raw values for the next panel
+      if (L::rowwarp(I) != warp || I <= j) continue;
+      double a0 = 0.0, a1 = 0.0;
+      if (j >= 0) { a0 = ch0[32 * I] * nd0; a1 = ch1[32 * I] * nd1; }
+#pragma unroll
+      for (int J2 = 0; J2 <= I; ++J2) {
+        if (J2 != j + 1) continue;
+        const int slot = L::slotbase(I) + J2;
+        if (J2 > 0) {
+          dmma884(acc[slot][0], acc[slot][1], a0, bn0);
+          dmma884(acc[slot][0], acc[slot][1], a1, bn1);
+        }
+        *reinterpret_cast<double2*>(praw + (8 * I + r) * PLD + 2 * q) = make_double2(acc[slot][0], acc[slot][1]);
+      }
+    }
+    if (warp == L::rowwarp(j + 1)) {  // look-ahead: factor diagonal block j+1 now
+      __syncwarp();
+      const int offA = L::chunk_off(2 * j + 2);
+      dm_diag_block<N, K, W>(sm, j + 1, dj + ((j + 1) & 1) * 16, offA, offA + (P - 8 * (j + 1)) * 4 + 4);
+    }
+    if (j >= 0) {
+#pragma unroll
+      for (int I = 2; I < NT; ++I) {  // pass B: the rest of the trailing matrix
+        if (L::rowwarp(I) != warp || I <= j + 1) continue;
+        const double a0 = ch0[32 * I] * nd0, a1 = ch1[32 * I] * nd1;
+#pragma unroll
+        for (int J2 = 2; J2 <= I; ++J2) {
+          if (J2 <= j + 1) continue;
+          const int slot = L::slotbase(I) + J2;
+          dmma884(acc[slot][0], acc[slot][1], a0, ch0[32 * J2]);
+          dmma884(acc[slot][0], acc[slot][1], a1, ch1[32 * J2]);
+        }
+      }
+    }
+    DM_T(1);
+    __syncthreads();
+    DM_T(2);
+  }
+  DM_T(6);
+  // ---- back substitution L' sol = w' (w' = D^-1 L^-1 rhs from the fused forward pass). Thread t = 8J + c first forms
+  //      column c of inv(L_JJ) in registers, so that finalising block J is an 8-term dot product of shuffled values. ----
+  double bacc = tid < P ? sm[L::O_WP + tid] : 0.0;
+  double tcol[8];
+  {
+    const int Jb = tid < P ? tid >> 3 : 0, c = tid & 7;
+    const int o0 = L::chunk_off(2 * Jb), o1 = o0 + (P - 8 * Jb) * 4 + 4;
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) {
+      double s0 = 0.0;
+#pragma unroll
+      for (int k2 = 0; k2 < rr; ++k2) s0 = fma(Lch[(k2 < 4 ? o0 : o1) + rr * 4 + (k2 & 3)], tcol[k2], s0);
+      tcol[rr] = rr < c ? 0.0 : (rr == c ? 1.0 : -s0);
+    }
+  }
+  const int mych = L::chunk_off(tid >> 2) + (tid & 3) - 32 * (tid >> 3);  // + 4*row gives L[row][tid]
+#pragma unroll 1
   for (int J = NT - 1; J >= 0; --J) {
     if (warp == (8 * J) / 32) {
       const int base = (8 * J) % 32, c = lane - base;
-      const bool mine = c >= 0 && c < 8;
+      double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-      for (int cc = 7; cc >= 1; --cc) {
-        const double xv = __shfl_sync(0xffffffffu, bacc, base + cc);
-        if (mine && c < cc) bacc = fma(-Lch[L::chunk_off(2 * J + (c >> 2)) + cc * 4 + (c & 3)], xv, bacc);
+      for (int rr = 0; rr < 8; rr += 2) {
+        s0 = fma(tcol[rr], __shfl_sync(0xffffffffu, bacc, base + rr), s0);
+        s1 = fma(tcol[rr + 1], __shfl_sync(0xffffffffu, bacc, base + rr + 1), s1);
       }
-      if (mine) sm[L::O_SOL + 8 * J + c] = bacc;
+      if (c >= 0 && c < 8) sm[L::O_SOL + 8 * J + c] = s0 + s1;
     }
     __syncthreads();
     if (tid < 8 * J) {
@@ -353,7 +426,21 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
     }
   }
   __syncthreads();
+  DM_T(7);
   return *failflag == 0;
+}
+
+// ComputeInitialGuess tail for variable v (qp.cc:462-481): clamp in list order (ClampX, qp.hpp:43-53),
+// s = max(1e-9, a x + b), z = 1/s.
+__device__ __forceinline__ void dm_clamp_init(double* X, double* S, double* Z, const double* IB, int v) {
+  double xv = X[v];
+  const double b0 = IB[2 * v], b1 = IB[2 * v + 1];
+  xv = xv > -b0 ? xv : -b0;
+  xv = xv < b1 ? xv : b1;
+  const double s0 = fmax(1.0e-9, xv + b0), s1 = fmax(1.0e-9, b1 - xv);
+  X[v] = xv;
+  S[2 * v] = s0; S[2 * v + 1] = s1;
+  Z[2 * v] = 1.0 / s0; Z[2 * v + 1] = 1.0 / s1;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -379,6 +466,7 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
   const double* const region = sm + L::O_REGION;
   const double tol2 = a.kkt_tol * a.kkt_tol, tau = 0.995;  // qp.cc:192
 
+  DM_T_INIT();
   for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
     const double* __restrict__ Gp = a.G + prob * (N * N);
     const double* __restrict__ Ap = K > 0 ? a.A + prob * (N * K) : nullptr;
@@ -390,42 +478,28 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
     for (int i = tid; i < M; i += THREADS) IB[i] = a.ib[prob * M + i];
     double acc[MAXS][2];
     int status = -1, iters = 0;
-    // ---- ComputeInitialGuess (qp.cc:439-482) ----
+    // ---- ComputeInitialGuess (qp.cc:439-482). SOLVE_EQUALITY_CONSTRAINED shares the factor/solve call site of the
+    //      Newton loop below (guess_pending): the KKT system without Sigma, rhs = -[c; b_eq]. ----
+    bool guess_pending = a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;
     if (a.guess == MO_GUESS_USER_PROVIDED) {
       for (int i = tid; i < N; i += THREADS) X[i] = vp[i];
       for (int i = tid; i < M; i += THREADS) { S[i] = vp[N + i]; Z[i] = vp[N + M + K + i]; }
       for (int i = tid; i < K; i += THREADS) Y[i] = vp[N + M + i];
-    } else {
-      if (a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED) {
-        cp_async_wait_all();
-        __syncthreads();
-        dm_assemble<N, K, W, MAXS>(acc, sm, false);
-        const double rhs = tid < N ? -sm[L::O_C + tid] : (tid < P ? -sm[L::O_B + tid - N] : 0.0);
-        const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm);
-        if (!ok) status = MO_QP_FAILED_FACTORIZATION;
-        dm_stage_issue<N, K, W>(sm + L::O_REGION, Gp, Ap);  // L overwrote the staged G
-        if (tid < N) X[tid] = ok ? SOL[tid] : 0.0;
-        else if (tid < P) Y[tid - N] = ok ? -SOL[tid] : 0.0;
-      }
+    } else if (!guess_pending) {
       __syncthreads();
-      if (tid < N) {  // clamp in list order (ClampX, qp.hpp:43-53), s = max(1e-9, a x + b), z = 1/s (qp.cc:462-481)
-        double xv = X[tid];
-        const double b0 = IB[2 * tid], b1 = IB[2 * tid + 1];
-        xv = xv > -b0 ? xv : -b0;
-        xv = xv < b1 ? xv : b1;
-        const double s0 = fmax(1.0e-9, xv + b0), s1 = fmax(1.0e-9, b1 - xv);
-        X[tid] = xv;
-        S[2 * tid] = s0; S[2 * tid + 1] = s1;
-        Z[2 * tid] = 1.0 / s0; Z[2 * tid + 1] = 1.0 / s1;
-      }
+      if (tid < N) dm_clamp_init(X, S, Z, IB, tid);
     }
     double mu = a.initial_mu, alpha_p = 1.0, alpha_d = 1.0;
     double kkt[4] = {0.0, 0.0, 0.0, 0.0};
     bool first = true;
     // ---- Solve loop (qp.cc:110-149); each trip = residuals of the current state, bookkeeping, one Newton step ----
     while (status < 0) {
+      DM_T(10);
       cp_async_wait_all();
       __syncthreads();
+      DM_T(11);
+      double rhs = tid < N ? -sm[L::O_C + tid] : (tid < P ? -sm[L::O_B + tid - N] : 0.0);  // guess: -[c; b_eq]
+      if (!guess_pending) {
       // (1) EvaluateKKTConditions (qp.cc:391-420): symmetric matvec from the staged lower trapezoid
       for (int task = tid; task < 2 * N + K; task += THREADS) {
         if (task < N) {  // row pass: c_i + sum_{j <= i} G(i,j) x_j
@@ -491,7 +565,9 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
         const double pe = RPE[tid - N];
         red[1] = pe * pe;
       }
+      DM_T(12);
       block_reduce<W, 6, false>(red, RED);
+      DM_T(13);
       // (3) bookkeeping of the Solve loop: errors of the step just taken, termination, barrier update
       const double mu_c = red[4] / (double)M;  // ComputeMu, qp.cc:509-516
       const double corrected = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
@@ -521,11 +597,20 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
         row[0] = sqrt(red[0]); row[1] = sqrt(cr > 0.0 ? cr : 0.0); row[2] = sqrt(red[1]); row[3] = sqrt(red[2]);
       }
       // (4) ComputeLDLT + SolveForUpdate: rhs = -[r_aug; r_pe]  ->  SOL = [dx; -dy]
-      const double rhs = tid < N ? -fma(-mu, T2[tid], T1[tid]) : (tid < P ? -RPE[tid - N] : 0.0);
-      dm_assemble<N, K, W, MAXS>(acc, sm, true);
+        rhs = tid < N ? -fma(-mu, T2[tid], T1[tid]) : (tid < P ? -RPE[tid - N] : 0.0);
+      }
+      DM_T(14);
+      dm_assemble<N, K, W, MAXS>(acc, sm, !guess_pending);
+      DM_T(15);
       const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm);
       if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
       dm_stage_issue<N, K, W>(sm + L::O_REGION, Gp, Ap);  // next trip's G, A: overlaps the update below
+      if (guess_pending) {  // x <- dx, y <- dy of the equality constrained solve (qp.cc:452-459), then clamp / s / z
+        guess_pending = false;
+        if (tid < N) { X[tid] = SOL[tid]; dm_clamp_init(X, S, Z, IB, tid); }
+        else if (tid < P) Y[tid - N] = -SOL[tid];
+        continue;
+      }
       // (5) ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199)
       double al[2] = {1.0, 1.0};
       double d0 = 0.0, d1 = 0.0, e0 = 0.0, e1 = 0.0;
@@ -577,6 +662,7 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
       }
     }
   }
+  DM_T_DUMP();
 }
 
 }  // namespace mo
