@@ -160,6 +160,77 @@ def workload_name(args):
             f"SOLVE_EQUALITY_CONSTRAINED guess, sigma=0.1, kkt_tol=1e-9, max 30 iterations")
 
 
+def ik_main(args, rank, world, local):
+    """BASELINE config 3: batch of transform-chain IK problems through mo_nls_solve_chain_ik_batch (device SQP + LM loop).
+    Metric: IP Newton steps/s inside the NLS solves (sum of QP iterations / time) and NLS problems/s."""
+    import torch
+    import torch.distributed as dist
+    from mini_opt_b200 import lib, nls
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib.load()
+    B = args.batch if args.batch != (1 << 20) else 100000
+    prm = synth.chain_ik_params()
+    if args.impl == "reference":
+        if rank == 0:
+            from oracle import oracle_py as O
+            sample = min(B, 20000)
+            ch = synth.chain_ik_batch_numpy(args.links, sample, seed=4321)
+            threads = host_cores()
+            O.nls_solve_chain("ref", synth.chain_ik_batch_numpy(args.links, 512, seed=1), prm, nthreads=threads)
+            t0 = time.perf_counter()
+            out, total = O.nls_solve_chain("ref", ch, prm, nthreads=threads)
+            dt = time.perf_counter() - t0
+            print(json.dumps({"impl": "reference", "metric": METRIC, "value": total / dt, "unit": UNIT, "n_gpus": args.gpus,
+                              "steps": 1, "warmup": 0, "ms_per_step": 1e3 * dt, "higher_is_better": True, "scaling": "weak",
+                              "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                              "config": {"workload": f"config3: {sample} chain-IK problems, {args.links} links (CPU sample)"},
+                              "nls_problems_per_sec": sample / dt,
+                              "cpu_baseline": {"value": total / dt, "unit": UNIT, "cores": threads, "kind": "reference",
+                                               "sample": f"{sample} problems, one ConstrainedNonlinearLeastSquares per std::thread"},
+                              "e2e": {"value": total / dt, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                              "gpu_launches": 0}), flush=True)
+        return
+    ch = nls.chain_to_device(synth.chain_ik_batch_numpy(args.links, B, seed=4321 + rank), dev)
+    out = nls.alloc_nls_out_torch(B, ch.n, dev)
+    stream = torch.cuda.current_stream(dev)
+    for _ in range(max(args.warmup, 3)):
+        nls.solve_chain_ik_device(ch, prm, out, dev, stream)
+    torch.cuda.synchronize()
+    l0 = lib.launch_count()
+    if world > 1:
+        dist.barrier()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        t0.record(stream)
+        for _ in range(args.steps):
+            nls.solve_chain_ik_device(ch, prm, out, dev, stream)
+        t1.record(stream)
+        torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / args.steps
+    qp_steps = float(out.qp_iterations.sum().item())
+    ok = float((out.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL).sum().item())
+    stats = torch.tensor([ms, qp_steps, ok], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx, sm_ = stats.clone(), stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sm_, op=dist.ReduceOp.SUM)
+        ms, qp_steps, ok = float(mx[0]), float(sm_[1]), float(sm_[2])
+    if rank == 0:
+        print(json.dumps({"metric": METRIC, "value": qp_steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                          "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                          "config": {"workload": f"config3: {B} transform-chain IK problems per GPU, {args.links} Z-revolute links, "
+                                                 "2 cost rows, joint limits +-pi/2, ARMIJO, max_qp_iterations=20, ModPi retraction",
+                                     "links": args.links, "batch_per_gpu": B},
+                          "nls_problems_per_sec": B * world / (ms * 1e-3), "absolute_tol_fraction": ok / (B * world),
+                          "gpu_launches": int(lib.launch_count() - l0), "clocks": clocks.summary()}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -170,12 +241,18 @@ def main():
     ap.add_argument("--k", type=int, default=2)
     ap.add_argument("--batch", type=int, default=1 << 20, help="problems per GPU")
     ap.add_argument("--cpu-sample", type=int, default=262144)
+    ap.add_argument("--workload", default="qp", choices=["qp", "ik"],
+                    help="qp: BASELINE config 2/4 (default); ik: config 3, transform-chain IK via the device SQP+LM loop")
+    ap.add_argument("--links", type=int, default=6, help="--workload ik: chain links (6-12)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "ik":
+        ik_main(args, rank, world, local)
+        return
     if args.impl == "reference":
         reference_arm(args, rank, world)
         return
@@ -247,9 +324,13 @@ def main():
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    # ncu dram__bytes_read.sum + dram__bytes_write.sum per pass of the default workload (profiles/r01_tpp_n8_ncu_full_summary.txt:
+    # guess kernel 0.894 + 0.328 GB, iterate kernel 1.247 + 0.364 GB); other shapes: not captured -> null
+    traffic = 2.833e9 if (n, k, B) == (8, 2, 1 << 20) else None
     roofline = {
-        "bound": "fp64", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak,
-        "traffic": None, "kernel": lib.kernel_variant(n, k, m, arrs.flags), "kernel_ms": kernel_ms,
+        "bound": "tensor", "pipe": "fp64: DFMA and DMMA.8x8x4 share one 64 FMA/clk/SM datapath (profiles/r01_dmma_vs_dfma_microbench.txt)",
+        "traffic": traffic, "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak,
+        "kernel": lib.kernel_variant(n, k, m, arrs.flags), "kernel_ms": kernel_ms,
         "flops_per_newton_step": F, "newton_steps_per_launch": steps_local,
         "peak_source": "DFMA microbenchmark measured live on this GPU (mo_measure_fp64_peak)",
         "hbm": {"achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",

@@ -1,0 +1,204 @@
+// C++ host API of mini_opt_b200: the reference's class surface for the QP hot path (gareth-cross/mini_opt,
+// include/mini_opt/qp.hpp:28-205, include/mini_opt/structs.hpp:24-134) over the C ABI of mini_opt_b200.h, plus the
+// batched entry point. Header only; link with -lminiopt_b200. No Eigen dependency: `Matrix` / `Vector` are minimal
+// column-major containers with Eigen::MatrixXd's storage order and accessors, so swapping the two aliases for
+// Eigen::MatrixXd / Eigen::VectorXd gives the drop-in described in INTEGRATION.md.
+#pragma once
+
+#include <cstdint>
+#include <optional>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "mini_opt_b200.h"
+
+namespace mini_opt_b200 {
+
+struct Vector : std::vector<double> {
+  using std::vector<double>::vector;
+  int rows() const { return static_cast<int>(size()); }
+};
+
+struct Matrix {  // column-major like Eigen::MatrixXd
+  Matrix() = default;
+  Matrix(int rows, int cols) : rows_(rows), cols_(cols), v_(static_cast<std::size_t>(rows) * cols, 0.0) {}
+  void resize(int rows, int cols) { rows_ = rows; cols_ = cols; v_.assign(static_cast<std::size_t>(rows) * cols, 0.0); }
+  double& operator()(int r, int c) { return v_[static_cast<std::size_t>(c) * rows_ + r]; }
+  double operator()(int r, int c) const { return v_[static_cast<std::size_t>(c) * rows_ + r]; }
+  int rows() const { return rows_; }
+  int cols() const { return cols_; }
+  const double* data() const { return v_.data(); }
+
+ private:
+  int rows_ = 0, cols_ = 0;
+  std::vector<double> v_;
+};
+
+// qp.hpp:28-70: a * x[variable] + b >= 0
+struct LinearInequalityConstraint {
+  int variable;
+  double a, b;
+  LinearInequalityConstraint(int variable_, double a_, double b_) : variable(variable_), a(a_), b(b_) {}
+  bool IsFeasible(double x) const { return a * x + b >= 0.0; }                        // qp.hpp:38-41
+  double ClampX(double x) const { return a < 0 ? (x < b / -a ? x : b / -a) : (x > -b / a ? x : -b / a); }  // qp.hpp:43-53
+  LinearInequalityConstraint ShiftTo(const Vector& x) const { return {variable, a, a * x[variable] + b}; }  // qp.hpp:57-59
+};
+
+// qp.hpp:77-92: Var(i) <= u, Var(i) >= l
+struct Var {
+  explicit Var(int variable_) : variable(variable_) {}
+  LinearInequalityConstraint operator<=(double value) const { return {variable, -1.0, value}; }
+  LinearInequalityConstraint operator>=(double value) const { return {variable, 1.0, -value}; }
+  int variable;
+};
+
+// qp.hpp:104-124: minimise 1/2 x'Gx + c'x  s.t.  A_eq x + b_eq = 0, a_i x[v_i] + b_i >= 0
+struct QP {
+  QP() = default;
+  explicit QP(int n) : G(n, n), c(static_cast<std::size_t>(n), 0.0) {}
+  Matrix G;
+  Vector c;
+  Matrix A_eq;
+  Vector b_eq;
+  std::vector<LinearInequalityConstraint> constraints;
+};
+
+enum class BarrierStrategy { COMPLEMENTARITY = 0, FIXED_DECREASE = 1, PREDICTOR_CORRECTOR = 2 };        // structs.hpp:24-31
+enum class InitialGuessMethod { NAIVE = 0, SOLVE_EQUALITY_CONSTRAINED = 1, USER_PROVIDED = 2 };          // structs.hpp:34-41
+enum class QPInteriorPointTerminationState { SATISFIED_KKT_TOL = 0, MAX_ITERATIONS = 1 };                // structs.hpp:97-102
+
+struct KKTError {  // structs.hpp:68-78
+  double r_dual = 0, r_comp = 0, r_primal_eq = 0, r_primal_ineq = 0;
+  double Max() const {
+    const double a = r_dual > r_comp ? r_dual : r_comp, b = r_primal_eq > r_primal_ineq ? r_primal_eq : r_primal_ineq;
+    return a > b ? a : b;
+  }
+};
+struct QPLagrangeMultipliers { double min, l_infinity; };  // structs.hpp:105-113
+
+struct FailedFactorization : std::runtime_error { using std::runtime_error::runtime_error; };  // qp.hpp:331-333
+
+// Per-problem result of the batched solve. `variables` = [x | s | y | z] (qp.cc:548-582).
+struct QPInteriorPointSolverOutputs {
+  QPInteriorPointTerminationState termination_state = QPInteriorPointTerminationState::MAX_ITERATIONS;
+  int num_iterations = 0;      // == iterations.size() of the reference's outputs
+  KKTError kkt_final;          // iterations.back().kkt_final
+  std::optional<QPLagrangeMultipliers> lagrange_multipliers;
+  int batch_status = MO_QP_MAX_ITERATIONS;  // MO_QP_*: 2 / 3 where the reference would have thrown
+  Vector variables;
+  int n = 0, k = 0, m = 0;
+  double x(int i) const { return variables[i]; }
+  double s(int i) const { return variables[n + i]; }
+  double y(int i) const { return variables[n + m + i]; }
+  double z(int i) const { return variables[n + m + k + i]; }
+};
+
+class QPInteriorPointSolver {
+ public:
+  struct Params {  // qp.hpp:134-164, same defaults
+    double initial_mu{1.0};
+    double sigma{0.5};
+    double termination_kkt_tol{1.0e-9};
+    double termination_complementarity_tol{1.0e-6};
+    int max_iterations{10};
+    BarrierStrategy barrier_strategy{BarrierStrategy::COMPLEMENTARITY};
+    bool decrease_mu_only_on_small_error{false};
+    InitialGuessMethod initial_guess_method{InitialGuessMethod::NAIVE};
+    bool initialize_mu_with_complementarity{false};
+  };
+
+  QPInteriorPointSolver() = default;
+  explicit QPInteriorPointSolver(const QP* problem) { Setup(problem); }
+
+  // qp.hpp:173-174: the problem is not copied and must outlive the solver.
+  void Setup(const QP* problem) {
+    if (!problem) throw std::invalid_argument("Must pass a non-null problem");
+    Check(*problem);
+    p_ = problem;
+  }
+
+  // One problem = a batch of one (host buffers; H2D, solve, D2H inside). Throws FailedFactorization like qp.cc:303-307.
+  QPInteriorPointSolverOutputs Solve(const Params& params, int device = 0) {
+    if (!p_) throw std::invalid_argument("Must have a valid problem");
+    std::vector<QPInteriorPointSolverOutputs> out = SolveBatch({*p_}, params, device);
+    if (out[0].batch_status == MO_QP_FAILED_FACTORIZATION) throw FailedFactorization("Failed to solve self-adjoint system");
+    if (out[0].batch_status == MO_QP_NONPOSITIVE_SLACK) throw std::runtime_error("Some slack variables s <= 0");
+    variables_ = out[0].variables;
+    return out[0];
+  }
+
+  const Vector& variables() const { return variables_; }
+  const QP& problem() const { return *p_; }
+
+  // Batched entry point: every problem must have the same (n, k, m). Per-problem failures are reported in
+  // `batch_status`, never thrown. `flags_box_pairs`: the constraints of every problem are the interleaved pairs
+  // Var(i) >= lo_i, Var(i) <= hi_i for i = 0..n-1 (selects the tuned kernels).
+  static std::vector<QPInteriorPointSolverOutputs> SolveBatch(const std::vector<QP>& qps, const Params& params,
+                                                              int device = 0) {
+    std::vector<QPInteriorPointSolverOutputs> result(qps.size());
+    if (qps.empty()) return result;
+    const int n = qps[0].G.rows(), k = qps[0].A_eq.rows(), m = static_cast<int>(qps[0].constraints.size());
+    const std::int64_t B = static_cast<std::int64_t>(qps.size()), stride = mo_qp_vars_stride(n, k, m);
+    std::vector<double> G(B * n * n), c(B * n), A(B * k * n + 1), b(B * k + 1), ia(B * m + 1), ib(B * m + 1);
+    std::vector<double> vars(B * stride), kkt(B * 4), lag(B * 2);
+    std::vector<std::int32_t> iv(B * m + 1), status(B), iters(B);
+    bool box = m == 2 * n;
+    for (std::int64_t p = 0; p < B; ++p) {
+      const QP& q = qps[p];
+      Check(q);
+      if (q.G.rows() != n || q.A_eq.rows() != k || static_cast<int>(q.constraints.size()) != m)
+        throw std::invalid_argument("SolveBatch needs problems of identical shape");
+      for (int i = 0; i < n * n; ++i) G[p * n * n + i] = q.G.data()[i];
+      for (int i = 0; i < n; ++i) c[p * n + i] = q.c[i];
+      for (int i = 0; i < k * n; ++i) A[p * k * n + i] = q.A_eq.data()[i];
+      for (int i = 0; i < k; ++i) b[p * k + i] = q.b_eq[i];
+      for (int i = 0; i < m; ++i) {
+        const LinearInequalityConstraint& con = q.constraints[i];
+        iv[p * m + i] = con.variable; ia[p * m + i] = con.a; ib[p * m + i] = con.b;
+        box = box && con.variable == i / 2 && con.a == ((i % 2 == 0) ? 1.0 : -1.0);
+      }
+    }
+    mo_qp_batch batch{n, k, m, box ? MO_QP_FLAG_BOX_PAIRS : 0, B, G.data(), c.data(), k ? A.data() : nullptr,
+                      k ? b.data() : nullptr, m ? iv.data() : nullptr, m ? ia.data() : nullptr, m ? ib.data() : nullptr,
+                      nullptr};
+    mo_qp_params prm;
+    mo_qp_params_default(&prm);
+    prm.initial_mu = params.initial_mu; prm.sigma = params.sigma;
+    prm.termination_kkt_tol = params.termination_kkt_tol;
+    prm.termination_complementarity_tol = params.termination_complementarity_tol;
+    prm.max_iterations = params.max_iterations; prm.barrier_strategy = static_cast<int>(params.barrier_strategy);
+    prm.decrease_mu_only_on_small_error = params.decrease_mu_only_on_small_error;
+    prm.initial_guess_method = static_cast<int>(params.initial_guess_method);
+    prm.initialize_mu_with_complementarity = params.initialize_mu_with_complementarity;
+    mo_qp_out out{vars.data(), status.data(), iters.data(), kkt.data(), lag.data(), nullptr};
+    const int rc = mo_qp_ip_solve_batch_host(&batch, &prm, &out, device);
+    if (rc == MO_ERR_INVALID_PARAMS) throw std::invalid_argument("invalid QPInteriorPointSolver::Params (qp.cc:76-82)");
+    if (rc == MO_ERR_INVALID_ARGUMENT) throw std::invalid_argument("invalid problem");
+    if (rc != MO_OK) throw std::runtime_error(std::string("mini_opt_b200 error ") + std::to_string(rc) + ": " + mo_last_error_string());
+    for (std::int64_t p = 0; p < B; ++p) {
+      QPInteriorPointSolverOutputs& o = result[p];
+      o.batch_status = status[p];
+      o.termination_state = status[p] == MO_QP_SATISFIED_KKT_TOL ? QPInteriorPointTerminationState::SATISFIED_KKT_TOL
+                                                                 : QPInteriorPointTerminationState::MAX_ITERATIONS;
+      o.num_iterations = iters[p];
+      o.kkt_final = KKTError{kkt[4 * p], kkt[4 * p + 1], kkt[4 * p + 2], kkt[4 * p + 3]};
+      if (k > 0) o.lagrange_multipliers = QPLagrangeMultipliers{lag[2 * p], lag[2 * p + 1]};
+      o.variables.assign(vars.begin() + p * stride, vars.begin() + (p + 1) * stride);
+      o.n = n; o.k = k; o.m = m;
+    }
+    return result;
+  }
+
+ private:
+  static void Check(const QP& q) {  // Setup's assertions, qp.cc:20-44
+    if (q.G.rows() != q.G.cols() || q.G.rows() != q.c.rows() || q.G.rows() <= 0) throw std::invalid_argument("G must be square and match c");
+    if (q.A_eq.rows() != q.b_eq.rows() || (q.A_eq.rows() > 0 && q.A_eq.cols() != q.G.rows())) throw std::invalid_argument("A_eq / b_eq mismatch");
+    for (const LinearInequalityConstraint& con : q.constraints)
+      if (con.variable < 0 || con.variable >= q.G.rows()) throw std::invalid_argument("constraint index out of bounds");
+  }
+  const QP* p_ = nullptr;
+  Vector variables_;
+};
+
+}  // namespace mini_opt_b200
