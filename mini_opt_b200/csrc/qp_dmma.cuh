@@ -19,6 +19,7 @@
 //     life of the problem) into the region L will overwrite: packed trapezoid columns padded so that both the
 //     fragment loads and the thread-per-row symmetric matvec are bank-conflict free.
 #pragma once
+#include <type_traits>
 
 #include "qp_common.cuh"
 
@@ -85,7 +86,9 @@ struct DmLayout {
   static constexpr int O_WP = O_DALL + P;             // forward-solved, D^-1-scaled rhs
   static constexpr int O_SOL = O_WP + P;              // solution [dx; -dy]
   static constexpr int O_RED = O_SOL + P;             // reductions: 8 values x W warps (+ flags)
-  static constexpr int TOTAL = O_RED + 8 * W + 8;
+  static constexpr int O_ONES = O_RED + 8 * W + 8;    // 8 x 1.0 and an 8x8 identity (row stride PLD): let the threads that
+  static constexpr int O_EYE = O_ONES + 8;            // invert L_jj run the P3 row recurrence without a divergent path
+  static constexpr int TOTAL = O_EYE + 8 * PLD;
   static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
 };
 
@@ -175,9 +178,9 @@ __device__ __forceinline__ void dm_stage_issue(double* __restrict__ region, cons
 
 // Reduced KKT matrix [[G + Sigma, .],[A, 0]] (ComputeLDLT assembly, qp.cc:289-297) into accumulator fragments.
 template <int N, int K, int W, int MAXS>
-__device__ __forceinline__ void dm_assemble(double (&acc)[MAXS][2], const double* __restrict__ sm, bool with_sigma) {
+__device__ __forceinline__ void dm_assemble(double (&acc)[MAXS][2], const double* __restrict__ sm, bool with_sigma, int tid) {
   using L = DmLayout<N, K, W>;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, r = lane >> 2, q = lane & 3;
+  const int lane = tid & 31, warp = tid >> 5, r = lane >> 2, q = lane & 3;
   const double* __restrict__ region = sm + L::O_REGION;
 #pragma unroll
   for (int I = 0; I < L::NT; ++I) {
@@ -187,8 +190,7 @@ __device__ __forceinline__ void dm_assemble(double (&acc)[MAXS][2], const double
       const int slot = L::slotbase(I) + J;
       double c0 = 0.0, c1 = 0.0;
       if (I < L::NTN) {
-        constexpr int dummy = 0; (void)dummy;
-        const int len = N - 8 * J + 2;
+          const int len = N - 8 * J + 2;
         const int base = L::gcol_off(8 * J) + 8 * (I - J) + r;
         c0 = region[base + (2 * q) * len];
         c1 = region[base + (2 * q + 1) * len];
@@ -265,6 +267,69 @@ __device__ __forceinline__ void dm_diag_block(double* __restrict__ sm, int j, do
   if (!ok && lane == 0) *reinterpret_cast<int*>(sm + L::O_RED + 8 * W) = 1;
 }
 
+// Trailing update of panel j = C - 1 with the panel index STATIC (dispatched by dm_switch below): the accumulator slots
+// are register names, so a runtime j would force every one of the NT(NT+1)/2 tile bodies to be issued predicated-off on
+// every panel (measured: 1000 of the 3400 cycles of a panel). Pass A updates and spills tile column C (raw values for
+// P3 / the look-ahead diagonal block), pass B updates the columns right of it.
+// f(integral_constant<int, c>) for the runtime c in [0, NT): one jump, static tile code behind it.
+template <int NT, class F>
+__device__ __forceinline__ void dm_switch(int c, F&& f) {
+#define DM_CASE(V) case V: if constexpr (V < NT) f(std::integral_constant<int, V>{}); break;
+  switch (c) { DM_CASE(0) DM_CASE(1) DM_CASE(2) DM_CASE(3) DM_CASE(4) DM_CASE(5) DM_CASE(6) DM_CASE(7) DM_CASE(8) DM_CASE(9)
+               DM_CASE(10) DM_CASE(11) DM_CASE(12) DM_CASE(13) DM_CASE(14) DM_CASE(15) default: break; }
+#undef DM_CASE
+  static_assert(NT <= 16, "extend dm_switch");
+}
+
+template <int N, int K, int W, int WARP, int C, int MAXS>
+__device__ __forceinline__ void dm_pass_a(double (&acc)[MAXS][2], const double* __restrict__ ch0, const double* __restrict__ ch1,
+                                          double nd0, double nd1, double* __restrict__ praw, int r, int q) {
+  using L = DmLayout<N, K, W>;
+  if constexpr (C > 0) {
+    const double bn0 = ch0[32 * C], bn1 = ch1[32 * C];  // B fragments of tile column C
+    double a0[L::NT], a1[L::NT];
+#pragma unroll
+    for (int I = C; I < L::NT; ++I)
+      if (L::rowwarp(I) == WARP) { a0[I] = ch0[32 * I] * nd0; a1[I] = ch1[32 * I] * nd1; }
+    // the two k-halves of a tile are dependent DMMAs: all first halves, then all second halves
+#pragma unroll
+    for (int I = C; I < L::NT; ++I)
+      if (L::rowwarp(I) == WARP) dmma884(acc[L::slotbase(I) + C][0], acc[L::slotbase(I) + C][1], a0[I], bn0);
+#pragma unroll
+    for (int I = C; I < L::NT; ++I)
+      if (L::rowwarp(I) == WARP) dmma884(acc[L::slotbase(I) + C][0], acc[L::slotbase(I) + C][1], a1[I], bn1);
+  }
+#pragma unroll
+  for (int I = C; I < L::NT; ++I)
+    if (L::rowwarp(I) == WARP)
+      *reinterpret_cast<double2*>(praw + (8 * I + r) * L::PLD + 2 * q) =
+          make_double2(acc[L::slotbase(I) + C][0], acc[L::slotbase(I) + C][1]);
+}
+
+template <int N, int K, int W, int WARP, int C, int MAXS>
+__device__ __forceinline__ void dm_pass_b(double (&acc)[MAXS][2], const double* __restrict__ ch0, const double* __restrict__ ch1,
+                                          double nd0, double nd1) {
+  using L = DmLayout<N, K, W>;
+  if constexpr (C > 0) {
+#pragma unroll
+    for (int I = C + 1; I < L::NT; ++I) {
+      if (L::rowwarp(I) != WARP) continue;
+      const double a0 = ch0[32 * I] * nd0, a1 = ch1[32 * I] * nd1;
+#pragma unroll
+      for (int J2 = C + 1; J2 <= I; ++J2) dmma884(acc[L::slotbase(I) + J2][0], acc[L::slotbase(I) + J2][1], a0, ch0[32 * J2]);
+#pragma unroll
+      for (int J2 = C + 1; J2 <= I; ++J2) dmma884(acc[L::slotbase(I) + J2][0], acc[L::slotbase(I) + J2][1], a1, ch1[32 * J2]);
+    }
+  }
+}
+
+// f(integral_constant<int, warp>, integral_constant<int, c>) for the runtime (warp, c): one jump, static tile code
+// behind it (each tile body exists once: it belongs to one warp and one column).
+template <int W, int NT, class F>
+__device__ __forceinline__ void dm_switch2(int warp, int c, F&& f) {
+  dm_switch<W>(warp, [&](auto ww) { dm_switch<NT>(c, [&](auto cc) { f(ww, cc); }); });
+}
+
 // Unpivoted LDL' of the matrix held in `acc` (right-looking, 8-column panels, DMMA trailing updates) fused with the
 // forward substitution of the right-hand side `racc` (thread t < P holds entry t), then the back substitution.
 // On return sm[O_SOL .. O_SOL+P) = K^-1 rhs for every thread to read. Returns false (uniformly) on a zero or
@@ -276,10 +341,10 @@ __device__ __forceinline__ void dm_diag_block(double* __restrict__ sm, int j, do
 // loop (tile loops stay unrolled so that the accumulators keep static register names): fully unrolled it is 0.5 MB of
 // SASS. j = -1 is the prologue (spill column 0, factor block 0).
 template <int N, int K, int W, int MAXS>
-__device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double racc, double* __restrict__ sm) {
+__device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double racc, double* __restrict__ sm, int tid) {
   using L = DmLayout<N, K, W>;
   constexpr int P = L::P, NT = L::NT, PLD = L::PLD;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = lane >> 2, q = lane & 3;
+  const int lane = tid & 31, warp = tid >> 5, r = lane >> 2, q = lane & 3;
   double* __restrict__ Lch = sm + L::O_REGION;
   double* __restrict__ praw = sm + L::O_PRAW;
   double* __restrict__ dj = sm + L::O_DJ;  // [0..31] d, 1/d of the panel (double buffered), [32..39] rhs block, [40..47] w
@@ -292,19 +357,20 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
     const double* __restrict__ djc = dj + (j & 1) * 16;
     const bool is_row = tid >= 8 * (j + 1) && tid < P;
     if (j >= 0) {
-      // ---- P3: triangular solve, one thread per row below the block; the last thread carries the right-hand side ----
-      const bool is_rhs = tid == L::THREADS - 1;
-      if (is_row || is_rhs) {
+      // ---- P3: triangular solve, one thread per row below the block; the last thread carries the right-hand side.
+      //      The 8 threads of block j itself run the same recurrence on a unit vector: thread 8j + c gets column c of
+      //      inv(L_jj) (for the back substitution) at no extra issue cost, parked in its dead row of praw. ----
+      const bool is_rhs = tid == L::THREADS - 1, is_inv = tid >= 8 * j && tid < 8 * j + 8;
+      if (is_row || is_inv || is_rhs) {  // one instruction stream for the three roles: only the pointers differ
+        const double* __restrict__ src = is_rhs ? dj + 32 : (is_inv ? sm + L::O_EYE + (tid & 7) * PLD : praw + tid * PLD);
+        const double* __restrict__ sc = is_inv ? sm + L::O_ONES : djc + 8;
+        double* __restrict__ d0 = is_rhs ? sm + L::O_WP + 8 * j : (is_inv ? praw + tid * PLD : Lch + off0 + (tid - 8 * j) * 4);
+        double* __restrict__ d1 = is_row ? Lch + off1 + (tid - 8 * j) * 4 : d0 + 4;
         double a[8], u[8];
-        if (is_row) {
 #pragma unroll
-          for (int c = 0; c < 8; c += 2) {
-            const double2 v = *reinterpret_cast<const double2*>(praw + tid * PLD + c);
-            a[c] = v.x; a[c + 1] = v.y;
-          }
-        } else {
-#pragma unroll
-          for (int c = 0; c < 8; ++c) a[c] = dj[32 + c];
+        for (int c = 0; c < 8; c += 2) {
+          const double2 v = *reinterpret_cast<const double2*>(src + c);
+          a[c] = v.x; a[c + 1] = v.y;
         }
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
@@ -312,18 +378,15 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
 #pragma unroll
           for (int k2 = 0; k2 < c; ++k2) v = fma(-u[k2], Lch[(k2 < 4 ? off0 : off1) + c * 4 + (k2 & 3)], v);
           u[c] = v;
-          l[c] = v * djc[8 + c];
+          l[c] = v * sc[c];
         }
-        if (is_row) {
-          double* d0 = Lch + off0 + (tid - 8 * j) * 4;
-          double* d1 = Lch + off1 + (tid - 8 * j) * 4;
-          *reinterpret_cast<double2*>(d0) = make_double2(l[0], l[1]);
-          *reinterpret_cast<double2*>(d0 + 2) = make_double2(l[2], l[3]);
-          *reinterpret_cast<double2*>(d1) = make_double2(l[4], l[5]);
-          *reinterpret_cast<double2*>(d1 + 2) = make_double2(l[6], l[7]);
-        } else {
+        *reinterpret_cast<double2*>(d0) = make_double2(l[0], l[1]);
+        *reinterpret_cast<double2*>(d0 + 2) = make_double2(l[2], l[3]);
+        *reinterpret_cast<double2*>(d1) = make_double2(l[4], l[5]);
+        *reinterpret_cast<double2*>(d1 + 2) = make_double2(l[6], l[7]);
+        if (is_rhs) {
 #pragma unroll
-          for (int c = 0; c < 8; ++c) { sm[L::O_WP + 8 * j + c] = l[c]; dj[40 + c] = u[c]; }
+          for (int c = 0; c < 8; c += 2) *reinterpret_cast<double2*>(dj + 40 + c) = make_double2(u[c], u[c + 1]);
         }
       }
       DM_T(3);
@@ -332,12 +395,11 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
       if (j == NT - 1) break;
     }
     // ---- P4: trailing update C(I,J') -= L(I,j) D_j L(J',j)' with DMMA; column j+1 first, then look-ahead ----
-    double nd0 = 0.0, nd1 = 0.0, bn0 = 0.0, bn1 = 0.0;
+    double nd0 = 0.0, nd1 = 0.0;
     const double* __restrict__ ch0 = Lch + off0 + r * 4 + q - 32 * j;  // + 32*I -> row 8I + r of chunk 2j
     const double* __restrict__ ch1 = Lch + off1 + r * 4 + q - 32 * j;
     if (j >= 0) {
       nd0 = -djc[q]; nd1 = -djc[4 + q];
-      if (j + 1 < NT) { bn0 = ch0[32 * (j + 1)]; bn1 = ch1[32 * (j + 1)]; }  // B fragments of tile column j+1
       if (is_row) {  // forward substitution of the right-hand side rows below the block
         double s0 = 0.0, s1 = 0.0;
 #pragma unroll
@@ -346,83 +408,70 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
       }
     }
     if (tid >= 8 * (j + 1) && tid < 8 * (j + 1) + 8) dj[32 + tid - 8 * (j + 1)] = racc;
-#pragma unroll
-    for (int I = 0; I < NT; ++I) {  // pass A: tiles of column j+1 -> update, spill raw values for the next panel
-      if (L::rowwarp(I) != warp || I <= j) continue;
-      double a0 = 0.0, a1 = 0.0;
-      if (j >= 0) { a0 = ch0[32 * I] * nd0; a1 = ch1[32 * I] * nd1; }
-#pragma unroll
-      for (int J2 = 0; J2 <= I; ++J2) {
-        if (J2 != j + 1) continue;
-        const int slot = L::slotbase(I) + J2;
-        if (J2 > 0) {
-          dmma884(acc[slot][0], acc[slot][1], a0, bn0);
-          dmma884(acc[slot][0], acc[slot][1], a1, bn1);
-        }
-        *reinterpret_cast<double2*>(praw + (8 * I + r) * PLD + 2 * q) = make_double2(acc[slot][0], acc[slot][1]);
-      }
-    }
+    // pass A: tiles of column j+1 -> update, spill raw values for the next panel
+    dm_switch2<W, NT>(warp, j + 1, [&](auto ww, auto cc) {
+      dm_pass_a<N, K, W, decltype(ww)::value, decltype(cc)::value>(acc, ch0, ch1, nd0, nd1, praw, r, q);
+    });
+    DM_T(8);
     if (warp == L::rowwarp(j + 1)) {  // look-ahead: factor diagonal block j+1 now
       __syncwarp();
       const int offA = L::chunk_off(2 * j + 2);
       dm_diag_block<N, K, W>(sm, j + 1, dj + ((j + 1) & 1) * 16, offA, offA + (P - 8 * (j + 1)) * 4 + 4);
+      DM_T(9);
     }
-    if (j >= 0) {
-#pragma unroll
-      for (int I = 2; I < NT; ++I) {  // pass B: the rest of the trailing matrix
-        if (L::rowwarp(I) != warp || I <= j + 1) continue;
-        const double a0 = ch0[32 * I] * nd0, a1 = ch1[32 * I] * nd1;
-#pragma unroll
-        for (int J2 = 2; J2 <= I; ++J2) {
-          if (J2 <= j + 1) continue;
-          const int slot = L::slotbase(I) + J2;
-          dmma884(acc[slot][0], acc[slot][1], a0, ch0[32 * J2]);
-          dmma884(acc[slot][0], acc[slot][1], a1, ch1[32 * J2]);
-        }
-      }
-    }
+    // pass B: the rest of the trailing matrix
+    dm_switch2<W, NT>(warp, j + 1, [&](auto ww, auto cc) {
+      dm_pass_b<N, K, W, decltype(ww)::value, decltype(cc)::value>(acc, ch0, ch1, nd0, nd1);
+    });
     DM_T(1);
     __syncthreads();
     DM_T(2);
   }
   DM_T(6);
-  // ---- back substitution L' sol = w' (w' = D^-1 L^-1 rhs from the fused forward pass). Thread t = 8J + c first forms
-  //      column c of inv(L_JJ) in registers, so that finalising block J is an 8-term dot product of shuffled values. ----
-  double bacc = tid < P ? sm[L::O_WP + tid] : 0.0;
-  double tcol[8];
-  {
-    const int Jb = tid < P ? tid >> 3 : 0, c = tid & 7;
-    const int o0 = L::chunk_off(2 * Jb), o1 = o0 + (P - 8 * Jb) * 4 + 4;
+  // The factor is consumed: end the live range of the accumulators here (warps that own fewer tiles never rewrite
+  // some slots, so without this the compiler keeps all of them live through the residual / update phases).
 #pragma unroll
-    for (int rr = 0; rr < 8; ++rr) {
-      double s0 = 0.0;
-#pragma unroll
-      for (int k2 = 0; k2 < rr; ++k2) s0 = fma(Lch[(k2 < 4 ? o0 : o1) + rr * 4 + (k2 & 3)], tcol[k2], s0);
-      tcol[rr] = rr < c ? 0.0 : (rr == c ? 1.0 : -s0);
-    }
-  }
-  const int mych = L::chunk_off(tid >> 2) + (tid & 3) - 32 * (tid >> 3);  // + 4*row gives L[row][tid]
+  for (int s = 0; s < MAXS; ++s) { acc[s][0] = 0.0; acc[s][1] = 0.0; }
+  // ---- back substitution L' sol = w' (w' = D^-1 L^-1 rhs from the fused forward pass, in WP) by WARP 0 ALONE: every
+  //      block step is a short dependent chain, so CTA barriers between the steps cost more than the parallelism they
+  //      buy. Block J is finalised as x_J = inv(L_JJ)' b_J (columns of inv(L_JJ) parked in praw by P3), then rows
+  //      t < 8J (lane l carries t = l, l + 32, ...) are updated. A runtime loop: the code stays small. ----
+  if (warp == 0) {
+    double* __restrict__ WP = sm + L::O_WP;
+    double* __restrict__ SOLv = sm + L::O_SOL;
+    const int c8 = lane & 7;
 #pragma unroll 1
-  for (int J = NT - 1; J >= 0; --J) {
-    if (warp == (8 * J) / 32) {
-      const int base = (8 * J) % 32, c = lane - base;
-      double s0 = 0.0, s1 = 0.0;
+    for (int J = NT - 1; J >= 0; --J) {
+      const double* __restrict__ tcp = praw + (8 * J + c8) * PLD;
+      const double* __restrict__ bj = WP + 8 * J;
+      double x0 = 0.0, x1 = 0.0;
 #pragma unroll
       for (int rr = 0; rr < 8; rr += 2) {
-        s0 = fma(tcol[rr], __shfl_sync(0xffffffffu, bacc, base + rr), s0);
-        s1 = fma(tcol[rr + 1], __shfl_sync(0xffffffffu, bacc, base + rr + 1), s1);
+        const double2 t2 = *reinterpret_cast<const double2*>(tcp + rr);
+        const double2 b2 = *reinterpret_cast<const double2*>(bj + rr);
+        x0 = fma(t2.x, b2.x, x0);
+        x1 = fma(t2.y, b2.y, x1);
       }
-      if (c >= 0 && c < 8) sm[L::O_SOL + 8 * J + c] = s0 + s1;
-    }
-    __syncthreads();
-    if (tid < 8 * J) {
-      double s0 = 0.0, s1 = 0.0;
+      if (lane < 8) SOLv[8 * J + lane] = x0 + x1;
+      __syncwarp();
+      if (J == 0) break;
+      double sol[8];
 #pragma unroll
       for (int rr = 0; rr < 8; rr += 2) {
-        s0 = fma(Lch[mych + 4 * (8 * J + rr)], sm[L::O_SOL + 8 * J + rr], s0);
-        s1 = fma(Lch[mych + 4 * (8 * J + rr + 1)], sm[L::O_SOL + 8 * J + rr + 1], s1);
+        const double2 v = *reinterpret_cast<const double2*>(SOLv + 8 * J + rr);
+        sol[rr] = v.x; sol[rr + 1] = v.y;
       }
-      bacc -= s0 + s1;
+      for (int t = lane; t < 8 * J; t += 32) {
+        const double* __restrict__ lp = Lch + L::chunk_off(t >> 2) + (t & 3) - 32 * (t >> 3) + 32 * J;  // L[8J + rr][t]
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int rr = 0; rr < 8; rr += 2) {
+          s0 = fma(lp[4 * rr], sol[rr], s0);
+          s1 = fma(lp[4 * rr + 4], sol[rr + 1], s1);
+        }
+        WP[t] -= s0 + s1;
+      }
+      __syncwarp();
     }
   }
   __syncthreads();
@@ -452,7 +501,10 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
   static_assert(L::P < L::THREADS, "the last thread carries the right-hand side");
   constexpr int P = L::P, M = L::M, THREADS = L::THREADS, MAXS = L::maxslots(), STRIDE = N + 2 * M + K;
   extern __shared__ __align__(16) double sm[];
-  const int tid = threadIdx.x;
+  // Virtual thread index: the warp roles (tile rows, per-variable work, back substitution) are rotated by the CTA's
+  // residency slot so that co-resident CTAs do not pile their heavy warps onto the same SM sub-partition.
+  const int rot = W > 1 ? (blockIdx.x / (gridDim.x >= MINB ? gridDim.x / MINB : 1)) & (W - 1) : 0;
+  const int tid = ((((int)threadIdx.x >> 5) + rot) & (W - 1)) * 32 + ((int)threadIdx.x & 31);
   double* const X = sm + L::O_X;
   double* const Y = sm + L::O_Y;
   double* const S = sm + L::O_S;
@@ -467,6 +519,8 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
   const double tol2 = a.kkt_tol * a.kkt_tol, tau = 0.995;  // qp.cc:192
 
   DM_T_INIT();
+  if (tid < 8) sm[L::O_ONES + tid] = 1.0;
+  for (int i = tid; i < 8 * L::PLD; i += THREADS) sm[L::O_EYE + i] = (i / L::PLD == i % L::PLD) ? 1.0 : 0.0;
   for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
     const double* __restrict__ Gp = a.G + prob * (N * N);
     const double* __restrict__ Ap = K > 0 ? a.A + prob * (N * K) : nullptr;
@@ -600,9 +654,9 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
         rhs = tid < N ? -fma(-mu, T2[tid], T1[tid]) : (tid < P ? -RPE[tid - N] : 0.0);
       }
       DM_T(14);
-      dm_assemble<N, K, W, MAXS>(acc, sm, !guess_pending);
+      dm_assemble<N, K, W, MAXS>(acc, sm, !guess_pending, tid);
       DM_T(15);
-      const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm);
+      const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm, tid);
       if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
       dm_stage_issue<N, K, W>(sm + L::O_REGION, Gp, Ap);  // next trip's G, A: overlaps the update below
       if (guess_pending) {  // x <- dx, y <- dy of the equality constrained solve (qp.cc:452-459), then clamp / s / z

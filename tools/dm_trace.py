@@ -19,9 +19,11 @@ L.mo_debug_read_trace(buf, 2048)  # discard the first (cold) run
 qp.solve_batch_device(arrs, synth.solve_params(), out, dev); torch.cuda.synchronize()
 cnt = L.mo_debug_read_trace(buf, 2048)
 ev = [(buf[i] >> 8, buf[i] & 255) for i in range(cnt)]
-names = {(1, 2): "P1 spill->sync", (2, 3): "P2 diag block", (3, 4): "P3 trsm (warp0)", (4, 5): "P3 sync wait", (5, 1): "P4 update (warp0)",
-         (5, 6): "P4 last", (6, 7): "back substitution", (10, 11): "stage wait", (11, 12): "residual matvec+per-var", (12, 13): "reduce",
-         (13, 14): "bookkeeping", (14, 15): "assemble", (15, 1): "assemble->P1", (7, 10): "update+loop", (7, 14): "x", (11, 14): "guess rhs"}
+names = {(4, 8): "P4 pass A (warp0)", (8, 9): "look-ahead diag block (warp0 owner)", (9, 1): "P4 pass B after diag (warp0 owner)",
+         (8, 1): "P4 pass B (warp0 not owner)", (1, 2): "P4 barrier wait", (2, 3): "P3 trsm (warp0)", (3, 4): "P3 barrier wait",
+         (2, 8): "prologue pass A", (15, 8): "assemble->prologue spill", (4, 6): "last panel exit", (6, 16): "backsubst: inv(L_JJ) columns",
+         (16, 7): "backsubst: block loop", (10, 11): "stage wait", (11, 12): "residual matvec+per-var", (12, 13): "reduce",
+         (13, 14): "bookkeeping", (14, 15): "assemble", (7, 10): "update+loop", (11, 14): "guess rhs"}
 tot = collections.Counter(); num = collections.Counter()
 for (t0, a), (t1, b) in zip(ev, ev[1:]):
     tot[(a, b)] += t1 - t0; num[(a, b)] += 1
