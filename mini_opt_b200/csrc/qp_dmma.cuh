@@ -225,7 +225,10 @@ __device__ __forceinline__ void dm_diag_block(double* __restrict__ sm, int j, do
     const double2 v = *reinterpret_cast<const double2*>(praw + (8 * j + lr) * L::PLD + c);
     a[c] = v.x; a[c + 1] = v.y;
   }
-  bool ok = true;
+  // Pivot bookkeeping without branches: every lane computes the same pivots; lane c keeps (d_c, 1/d_c) by select and
+  // the 8 pairs are stored once at the end. A zero / non-finite pivot turns its reciprocal chain into NaN
+  // (rcp.approx(0) = inf, inf * 0 = NaN), which `chk` accumulates: one FMA per pivot instead of four compares.
+  double chk = 0.0, myd = 0.0, myinv = 0.0;
 #pragma unroll
   for (int c = 0; c < 8; c += 2) {
     const double a00 = __shfl_sync(0xffffffffu, a[c], c);
@@ -235,36 +238,27 @@ __device__ __forceinline__ void dm_diag_block(double* __restrict__ sm, int j, do
     const double inv0 = rcp_chain(a00), rdet = rcp_chain(det);
     const double inv1 = a00 * rdet;               // 1 / d1 with d1 = det / a00
     const double d1 = fma(-(a10 * inv0), a10, a11);
-    ok = ok && (fabs(a00) > 0.0) && (fabs(a00) <= 1.7976931348623157e308) && (fabs(d1) > 0.0) &&
-         (fabs(d1) <= 1.7976931348623157e308);
+    chk = fma(inv0, 0.0, chk);
+    chk = fma(inv1, 0.0, chk);
     const double u0 = a[c], l0 = u0 * inv0;
     const double u1 = fma(-l0, a10, a[c + 1]), l1 = u1 * inv1;
+    // (a 2x2 block-pivot form whose only post-reciprocal op is one FMA was tried: more issue slots, measured slower)
 #pragma unroll
     for (int c2 = c + 2; c2 < 8; ++c2) {
       const double v0 = __shfl_sync(0xffffffffu, u0, c2), v1 = __shfl_sync(0xffffffffu, u1, c2);
       a[c2] = fma(-l1, v1, fma(-l0, v0, a[c2]));
     }
-    if (lane == c) {
-      djb[c] = a00; djb[8 + c] = inv0; djb[c + 1] = d1; djb[9 + c] = inv1;
-      sm[L::O_DALL + 8 * j + c] = a00; sm[L::O_DALL + 8 * j + c + 1] = d1;
-    }
-    a[c] = l0; a[c + 1] = l1;
+    myd = lr == c ? a00 : (lr == c + 1 ? d1 : myd);
+    myinv = lr == c ? inv0 : (lr == c + 1 ? inv1 : myinv);
+    // unit lower L_jj, columns c, c+1 of row lr (chunk h = c / 4, 16-byte slot (c & 2))
+    const double w0 = lr > c ? l0 : (lr == c ? 1.0 : 0.0), w1 = lr > c + 1 ? l1 : (lr == c + 1 ? 1.0 : 0.0);
+    if (lane < 8) *reinterpret_cast<double2*>(Lch + (c >= 4 ? offB : offA) + lr * 4 + (c & 2)) = make_double2(w0, w1);
   }
   if (lane < 8) {
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      double v[4];
-#pragma unroll
-      for (int qq = 0; qq < 4; ++qq) {
-        const int c = 4 * h + qq;
-        v[qq] = c < lr ? a[c] : (c == lr ? 1.0 : 0.0);
-      }
-      double* dst = Lch + (h ? offB : offA) + lr * 4;
-      *reinterpret_cast<double2*>(dst) = make_double2(v[0], v[1]);
-      *reinterpret_cast<double2*>(dst + 2) = make_double2(v[2], v[3]);
-    }
+    djb[lr] = myd; djb[8 + lr] = myinv;
+    sm[L::O_DALL + 8 * j + lr] = myd;
   }
-  if (!ok && lane == 0) *reinterpret_cast<int*>(sm + L::O_RED + 8 * W) = 1;
+  if (chk != chk && lane == 0) *reinterpret_cast<int*>(sm + L::O_RED + 8 * W) = 1;
 }
 
 // Trailing update of panel j = C - 1 with the panel index STATIC (dispatched by dm_switch below): the accumulator slots
