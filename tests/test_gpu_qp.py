@@ -283,3 +283,49 @@ def test_full_size_properties(dev):
     qp.solve_batch_device(sub, prm, out2, dev)
     torch.cuda.synchronize()
     assert torch.equal(out2.vars, out.vars[:50000][perm]) and torch.equal(out2.iters, out.iters[:50000][perm])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,k,B", [(64, 16, 8192), (32, 8, 16384), (16, 8, 16384)])
+def test_dmma_shapes_properties_and_determinism(dev, n, k, B):
+    """CTA-per-problem DMMA kernel at a batch that fills every SM with its full residency (4+ CTAs per SM, rotated
+    warp roles): KKT residuals recomputed on the host side in torch, and bit-identical results across repeated runs
+    and under a batch permutation (a shared-memory race or state leaking between the problems of a persistent CTA
+    shows up as nondeterminism)."""
+    import torch
+    from mini_opt_b200 import qp, lib
+    m = 2 * n
+    arrs = synth.box_qp_batch_torch(n, k, B, seed=11, device=dev)
+    prm = synth.solve_params()
+    assert lib.load().mo_qp_kernel_variant(n, k, m, arrs.flags).decode() == "dmma"
+    outs = []
+    for _ in range(3):
+        out = qp.alloc_out_torch(B, n, k, m, dev)
+        qp.solve_batch_device(arrs, prm, out, dev)
+        torch.cuda.synchronize()
+        outs.append(out)
+    for o in outs[1:]:
+        assert torch.equal(o.vars, outs[0].vars) and torch.equal(o.iters, outs[0].iters) and torch.equal(o.status, outs[0].status)
+    out = outs[0]
+    status = out.status.cpu().numpy()
+    assert np.isin(status, [0, 1]).all() and (status == 0).mean() > 0.99
+    ok = out.status == 0
+    x, s = out.vars[:, :n], out.vars[:, n:n + m]
+    y, z = out.vars[:, n + m:n + m + k], out.vars[:, n + m + k:]
+    G = torch.tril(arrs.G.transpose(1, 2))
+    Gs = G + torch.tril(G, -1).transpose(1, 2)
+    A = arrs.A_eq.transpose(1, 2)
+    r_d = torch.einsum("bij,bj->bi", Gs, x) + arrs.c - torch.einsum("bki,bk->bi", A, y) - (z[:, 0::2] - z[:, 1::2])
+    r_pe = torch.einsum("bki,bi->bk", A, x) + arrs.b_eq
+    scale = 1.0 + float(arrs.c.abs().max())
+    assert float(r_d[ok].norm(dim=1).max()) < 1e-7 * scale and float(r_pe[ok].norm(dim=1).max()) < 1e-7 * scale
+    assert float(s[ok].min()) > 0 and float(z[ok].min()) > 0
+    nb = B // 4
+    perm = torch.randperm(nb, device=dev)
+    sub = abi.QPBatchArrays(n=n, k=k, m=m, batch=nb, G=arrs.G[:nb][perm].contiguous(), c=arrs.c[:nb][perm].contiguous(),
+                            A_eq=arrs.A_eq[:nb][perm].contiguous(), b_eq=arrs.b_eq[:nb][perm].contiguous(),
+                            ineq_b=arrs.ineq_b[:nb][perm].contiguous(), flags=arrs.flags)
+    out2 = qp.alloc_out_torch(nb, n, k, m, dev)
+    qp.solve_batch_device(sub, prm, out2, dev)
+    torch.cuda.synchronize()
+    assert torch.equal(out2.vars, out.vars[:nb][perm]) and torch.equal(out2.iters, out.iters[:nb][perm])
