@@ -131,8 +131,10 @@ __device__ __forceinline__ double rcp_chain(double d) {
 }
 
 // Sum / min over the CTA of NV values per thread; result broadcast to every thread. `red` holds NV*W doubles.
-template <int W, int NV, bool IS_MIN>
-__device__ __forceinline__ void block_reduce(double (&v)[NV], double* red) {
+// `between` runs between the two barriers of the reduction (work that needs the first barrier's visibility and whose
+// shared-memory reads must be complete, CTA-wide, when the reduction returns).
+template <int W, int NV, bool IS_MIN, class F>
+__device__ __forceinline__ void block_reduce(double (&v)[NV], double* red, F&& between) {
 #pragma unroll
   for (int i = 0; i < NV; ++i)
 #pragma unroll
@@ -140,12 +142,18 @@ __device__ __forceinline__ void block_reduce(double (&v)[NV], double* red) {
       const double t = __shfl_xor_sync(0xffffffffu, v[i], o);
       v[i] = IS_MIN ? fmin(v[i], t) : v[i] + t;
     }
-  if (W == 1) return;
+  if (W == 1) {
+    __syncwarp();
+    between();
+    __syncwarp();
+    return;
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __syncthreads();
   if (lane == 0)
 #pragma unroll
     for (int i = 0; i < NV; ++i) red[warp * NV + i] = v[i];
+  between();
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
@@ -154,6 +162,10 @@ __device__ __forceinline__ void block_reduce(double (&v)[NV], double* red) {
     for (int w = 1; w < W; ++w) t = IS_MIN ? fmin(t, red[w * NV + i]) : t + red[w * NV + i];
     v[i] = t;
   }
+}
+template <int W, int NV, bool IS_MIN>
+__device__ __forceinline__ void block_reduce(double (&v)[NV], double* red) {
+  block_reduce<W, NV, IS_MIN>(v, red, [] {});
 }
 
 // cp.async staging of the problem's G (lower trapezoid) and A_eq into the region L will later overwrite.
@@ -343,7 +355,6 @@ __device__ __forceinline__ bool dm_factor_solve(double (&acc)[MAXS][2], double r
   double* __restrict__ praw = sm + L::O_PRAW;
   double* __restrict__ dj = sm + L::O_DJ;  // [0..31] d, 1/d of the panel (double buffered), [32..39] rhs block, [40..47] w
   int* failflag = reinterpret_cast<int*>(sm + L::O_RED + 8 * W);
-  if (tid == 0) *failflag = 0;
   double l[8];
 #pragma unroll 1
   for (int j = -1; j < NT; ++j) {
@@ -614,7 +625,11 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
         red[1] = pe * pe;
       }
       DM_T(12);
-      block_reduce<W, 6, false>(red, RED);
+      // The KKT assembly rides between the two barriers of the reduction: Sigma is visible after the first, and the
+      // second guarantees every warp is done reading the staged G, A before the owner of tile row 0 writes L_00 over
+      // them in the factorization prologue (a problem that terminates below wastes one assembly).
+      if (tid == 0) *reinterpret_cast<int*>(sm + L::O_RED + 8 * W) = 0;  // zero-pivot flag of the coming factorization
+      block_reduce<W, 6, false>(red, RED, [&] { dm_assemble<N, K, W, MAXS>(acc, sm, true, tid); });
       DM_T(13);
       // (3) bookkeeping of the Solve loop: errors of the step just taken, termination, barrier update
       const double mu_c = red[4] / (double)M;  // ComputeMu, qp.cc:509-516
@@ -648,7 +663,11 @@ __global__ void __launch_bounds__(32 * W, MINB) qp_dm_kernel(const QPArgs a) {
         rhs = tid < N ? -fma(-mu, T2[tid], T1[tid]) : (tid < P ? -RPE[tid - N] : 0.0);
       }
       DM_T(14);
-      dm_assemble<N, K, W, MAXS>(acc, sm, !guess_pending, tid);
+      if (guess_pending) {  // KKT system without Sigma (the Newton trips assemble inside the reduction above)
+        if (tid == 0) *reinterpret_cast<int*>(sm + L::O_RED + 8 * W) = 0;
+        dm_assemble<N, K, W, MAXS>(acc, sm, false, tid);
+        __syncthreads();
+      }
       DM_T(15);
       const bool ok = dm_factor_solve<N, K, W, MAXS>(acc, rhs, sm, tid);
       if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
