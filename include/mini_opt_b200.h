@@ -158,6 +158,10 @@ int mo_qp_ip_newton_step_batch(const mo_qp_batch* problems, double mu, int32_t b
 
 /* LineSearchStrategy, include/mini_opt/structs.hpp:146-151 */
 enum { MO_LS_ARMIJO_BACKTRACK = 0, MO_LS_POLYNOMIAL_APPROXIMATION = 1 };
+/* Inner QP solver of mo_nls_solve_chain_ik_batch: AUTO = warp-synchronous register solver (unpivoted LDL') when
+ * n + k <= 16, m <= 32 and no variable carries more than two constraints, else GENERIC; GENERIC = the Eigen-pivot-order
+ * solver of the generic QP kernel (audit path: reproduces the reference's QP iteration counts most closely). */
+enum { MO_NLS_QP_AUTO = 0, MO_NLS_QP_GENERIC = 1 };
 /* NLSTerminationState, include/mini_opt/structs.hpp:233-248 */
 enum {
   MO_NLS_MAX_ITERATIONS = 0,
@@ -197,7 +201,7 @@ typedef struct mo_nls_params {
   double max_lambda;
   double min_lambda;
   int32_t retraction; /* MO_RETRACT_* */
-  int32_t reserved;
+  int32_t inner_qp_solver; /* MO_NLS_QP_* */
 } mo_nls_params;
 
 void mo_nls_params_default(mo_nls_params* p);

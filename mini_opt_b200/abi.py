@@ -225,7 +225,7 @@ class MoNlsParams(C.Structure):
         ("max_lambda", C.c_double),
         ("min_lambda", C.c_double),
         ("retraction", C.c_int32),
-        ("reserved", C.c_int32),
+        ("inner_qp_solver", C.c_int32),
     ]
 
 
@@ -252,6 +252,7 @@ class NLSParams:
     max_lambda: float = 1.0
     min_lambda: float = 0.0
     retraction: int = MO_RETRACT_ADD
+    inner_qp_solver: int = 0  # MO_NLS_QP_AUTO; 1 = MO_NLS_QP_GENERIC
 
     def to_c(self) -> MoNlsParams:
         return MoNlsParams(
@@ -260,7 +261,7 @@ class NLSParams:
             int(self.max_line_search_iterations), int(self.line_search_strategy), self.armijo_search_tau,
             self.equality_penalty_initial, self.equality_penalty_scale_factor, self.equality_penalty_rho,
             self.lambda_initial, self.lambda_failure_init, self.lambda_decrease_on_success,
-            self.lambda_decrease_on_restore, self.max_lambda, self.min_lambda, int(self.retraction), 0)
+            self.lambda_decrease_on_restore, self.max_lambda, self.min_lambda, int(self.retraction), int(self.inner_qp_solver))
 
 
 class MoNlsLinearizeArgs(C.Structure):

@@ -516,7 +516,8 @@ int check_nls_params(const mo_nls_params* p) {
       p->lambda_failure_init >= 0 && p->lambda_decrease_on_success >= 0 && p->lambda_decrease_on_success < 1.0 &&
       p->lambda_decrease_on_restore >= 0 && p->lambda_decrease_on_restore < 1.0 &&
       (p->line_search_strategy == MO_LS_ARMIJO_BACKTRACK || p->line_search_strategy == MO_LS_POLYNOMIAL_APPROXIMATION) &&
-      (p->retraction == MO_RETRACT_ADD || p->retraction == MO_RETRACT_MOD_PI) && p->max_line_search_iterations < 40;
+      (p->retraction == MO_RETRACT_ADD || p->retraction == MO_RETRACT_MOD_PI) && p->max_line_search_iterations < 40 &&
+      (p->inner_qp_solver == MO_NLS_QP_AUTO || p->inner_qp_solver == MO_NLS_QP_GENERIC);
   return ok ? MO_OK : MO_ERR_INVALID_PARAMS;
 }
 
@@ -570,7 +571,7 @@ void mo_nls_params_default(mo_nls_params* p) {  // nonlinear.hpp:37-124
   p->armijo_search_tau = 0.8; p->equality_penalty_initial = 1.0; p->equality_penalty_scale_factor = 1.01;
   p->equality_penalty_rho = 0.1; p->lambda_initial = 0.0; p->lambda_failure_init = 1.0e-2;
   p->lambda_decrease_on_success = 0.1; p->lambda_decrease_on_restore = 0.8; p->max_lambda = 1.0; p->min_lambda = 0.0;
-  p->retraction = MO_RETRACT_ADD; p->reserved = 0;
+  p->retraction = MO_RETRACT_ADD; p->inner_qp_solver = MO_NLS_QP_AUTO;
 }
 
 int mo_nls_linearize_batch(const mo_nls_linearize_args* g, int device, void* cuda_stream) {
@@ -648,7 +649,7 @@ int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_
                         params->equality_penalty_initial, params->equality_penalty_scale_factor,
                         params->equality_penalty_rho, params->lambda_initial, params->lambda_failure_init,
                         params->lambda_decrease_on_success, params->lambda_decrease_on_restore, params->max_lambda,
-                        params->min_lambda, params->retraction};
+                        params->min_lambda, params->retraction, params->inner_qp_solver};
   const mo::NlsOut o{out->x, out->termination, out->iterations, out->qp_iterations, out->ls_steps, out->errors};
   mo::nls_chain_ik_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(problems), p, o);
   g_launches.fetch_add(1);

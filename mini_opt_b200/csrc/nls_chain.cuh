@@ -11,6 +11,7 @@
 #pragma once
 
 #include "qp_generic.cuh"
+#include "qp_warp.cuh"
 
 namespace mo {
 
@@ -38,7 +39,7 @@ struct NlsParams {  // mo_nls_params
   int max_line_search_iterations, line_search_strategy;
   double armijo_search_tau, equality_penalty_initial, equality_penalty_scale_factor, equality_penalty_rho;
   double lambda_initial, lambda_failure_init, lambda_decrease_on_success, lambda_decrease_on_restore, max_lambda, min_lambda;
-  int retraction;
+  int retraction, inner_qp_solver;
 };
 
 struct NlsOut {
@@ -417,7 +418,10 @@ __host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost,
 }
 
 // ConstrainedNonlinearLeastSquares::Solve (nonlinear.cc:75-158), one warp (= one 32-thread block) per problem.
-__global__ void __launch_bounds__(32) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out) {
+#ifndef MO_IK_MINB
+#define MO_IK_MINB 24  // measured on B200 (6 links, 100K problems): 8 -> 769 ms, 16 -> 672, 24 -> 641, 32 -> 682
+#endif
+__global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x, n = a.n, k = a.n_eq, m = a.m;
   ChainWork C;
@@ -462,7 +466,8 @@ __global__ void __launch_bounds__(32) nls_chain_ik_kernel(const ChainArgs a, con
       __syncwarp();
       int qiters = 0;
       double kkt_after[4];
-      const int qstatus = gen_solve<32>(W, Q, sp, nullptr, qiters, kkt_after);
+      int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve<16>(W, Q, sp, qiters, kkt_after);
+      if (qstatus < 0) qstatus = gen_solve<32>(W, Q, sp, nullptr, qiters, kkt_after);
       if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; }  // the reference throws here
       qp_total += qiters;
       for (int i = lane; i < n; i += 32) dx[i] = W.vars[i];
