@@ -466,7 +466,7 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
       __syncwarp();
       int qiters = 0;
       double kkt_after[4];
-      int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve<16>(W, Q, sp, qiters, kkt_after);
+      int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve_any(W, Q, sp, qiters, kkt_after);
       if (qstatus < 0) qstatus = gen_solve<32>(W, Q, sp, nullptr, qiters, kkt_after);
       if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; }  // the reference throws here
       qp_total += qiters;

@@ -112,31 +112,29 @@ __device__ int wip_solve(const GenWork& W, const GenProb& Q, const GenSolveParam
   const int ld = W.ld;
   double a[PMAX];
   double u = 0.0;  // x_lane or y_{lane-n}
-  // ---- ComputeInitialGuess (qp.cc:439-482) ----
-  if (prm.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED) {
-#pragma unroll
-    for (int j = 0; j < PMAX; ++j) a[j] = g[j];
-    double y = -lin;
-    if (!wip_factor_solve<PMAX>(a, p, Lsm, ld, y)) return MO_QP_FAILED_FACTORIZATION;
-    u = isx ? y : (isy ? -y : 0.0);
-  }
-  {  // clamp in list order (ClampX, qp.hpp:43-53), s = max(1e-9, a x + b), z = 1/s
+  double s = 1.0, z = 1.0;
+  // ComputeInitialGuess tail (qp.cc:462-481): clamp in list order (ClampX, qp.hpp:43-53), s = max(1e-9, a x + b), z = 1/s
+  auto clamp_init = [&]() {
     const double a0 = __shfl_sync(kFull, ca, s0), b0 = __shfl_sync(kFull, cb, s0);
     const double a1 = __shfl_sync(kFull, ca, s1), b1 = __shfl_sync(kFull, cb, s1);
     if (c0 >= 0) { if (a0 < 0) { const double hi = b0 / -a0; u = u < hi ? u : hi; } else { const double lo = -b0 / a0; u = u > lo ? u : lo; } }
     if (c1 >= 0) { if (a1 < 0) { const double hi = b1 / -a1; u = u < hi ? u : hi; } else { const double lo = -b1 / a1; u = u > lo ? u : lo; } }
-  }
-  double s = 1.0, z = 1.0;
-  {
     const double xv = __shfl_sync(kFull, u, cv);
     if (isc) { s = fmax(1.0e-9, fma(ca, xv, cb)); z = 1.0 / s; }
-  }
+  };
+  // SOLVE_EQUALITY_CONSTRAINED (qp.cc:452-459) shares the factor/solve call site of the Newton loop (guess_pending)
+  bool guess_pending = prm.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;
+  if (!guess_pending) clamp_init();
   // ---- Solve loop (qp.cc:110-149): each trip = residuals of the current point, bookkeeping, one Newton step ----
   double mu = prm.initial_mu;
   bool first = true;
   int status = MO_QP_MAX_ITERATIONS;
   const double minv = m > 0 ? 1.0 / (double)m : 0.0;
   for (;;) {
+    double y, sig = 0.0, rpi = 0.0, comp = 0.0, w = 0.0, is = 0.0, barrier = 0.0;
+    if (guess_pending) {
+      y = -lin;  // KKT system without Sigma, rhs = -[c; b_eq]
+    } else {
     // EvaluateKKTConditions (qp.cc:391-420)
     double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
@@ -146,7 +144,7 @@ __device__ int wip_solve(const GenWork& W, const GenProb& Q, const GenSolveParam
     }
     const double rmain = (acc0 + acc1) + lin;  // r_d before the inequality term (lanes < n), r_pe (lanes n..p)
     const double xv = __shfl_sync(kFull, u, cv);
-    const double rpi = isc ? fma(ca, xv, cb) - s : 0.0, comp = isc ? s * z : 0.0;
+    rpi = isc ? fma(ca, xv, cb) - s : 0.0; comp = isc ? s * z : 0.0;
     const double rd_all = scatter(rmain, ca * z, -1.0);  // (shuffles: every lane executes, then select)
     const double rd = isx ? rd_all : 0.0;
     // ComputeErrors (qp.cc:423-437), ComputeMu (:509-516)
@@ -169,16 +167,23 @@ __device__ int wip_solve(const GenWork& W, const GenProb& Q, const GenSolveParam
     if (prm.max_iterations <= 0) break;
     // ComputeLDLT (qp.cc:275-316)
     if (__any_sync(kFull, isc && !(s > 0.0))) { status = MO_QP_NONPOSITIVE_SLACK; break; }
-    const double w = isc ? z / s : 0.0, is = isc ? 1.0 / s : 0.0;
-    const double barrier = m > 0 ? mu : 0.0;  // Iterate solves with mu = 0 when there are no inequalities
-    const double sig = scatter(0.0, (ca * w) * ca, 1.0);  // 0 on lanes without constraints
+    w = isc ? z / s : 0.0; is = isc ? 1.0 / s : 0.0;
+    barrier = m > 0 ? mu : 0.0;  // Iterate solves with mu = 0 when there are no inequalities
+    sig = scatter(0.0, (ca * w) * ca, 1.0);  // 0 on lanes without constraints
     // SolveForUpdate (qp.cc:318-364)
     const double q = fma(ca * w, rpi, ca * (comp - barrier) * is);
     const double raug = scatter(rd, q, 1.0);
-    double y = isx ? -raug : (isy ? -rmain : 0.0);
+    y = isx ? -raug : (isy ? -rmain : 0.0);
+    }
 #pragma unroll
     for (int j = 0; j < PMAX; ++j) a[j] = g[j] + ((j == lane && isx) ? sig : 0.0);
     if (!wip_factor_solve<PMAX>(a, p, Lsm, ld, y)) { status = MO_QP_FAILED_FACTORIZATION; break; }
+    if (guess_pending) {
+      guess_pending = false;
+      u = isx ? y : (isy ? -y : 0.0);
+      clamp_init();
+      continue;
+    }
     const double dxv = __shfl_sync(kFull, y, cv);
     const double ds = isc ? fma(ca, dxv, rpi) : 0.0;
     const double dz = isc ? -w * ds - is * (comp - barrier) : 0.0;
@@ -196,6 +201,17 @@ __device__ int wip_solve(const GenWork& W, const GenProb& Q, const GenSolveParam
   if (isc) { W.vars[n + lane] = s; W.vars[n + m + k + lane] = z; }
   __syncwarp();
   return status;
+}
+
+// Smallest register tile that holds the problem: the unrolled column loops carry one uniform branch per column of
+// PMAX, so a 6x6 system runs through the PMAX = 8 instance, not through 16 columns of skipped code.
+__device__ __forceinline__ int wip_solve_any(const GenWork& W, const GenProb& Q, const GenSolveParams& prm, int& iters,
+                                             double (&kkt_after)[4]) {
+  const int p = W.n + W.k;
+  if (p <= 4) return wip_solve<4>(W, Q, prm, iters, kkt_after);
+  if (p <= 8) return wip_solve<8>(W, Q, prm, iters, kkt_after);
+  if (p <= 12) return wip_solve<12>(W, Q, prm, iters, kkt_after);
+  return wip_solve<16>(W, Q, prm, iters, kkt_after);
 }
 
 }  // namespace mo
