@@ -1,0 +1,512 @@
+// WARP-per-problem interior point QP solve for medium dense box-constrained QPs (n, k multiples of 8, n + k <= 80):
+// the reduced KKT matrix lives ONLY in shared memory as 8x8 tiles, the factorization is a LEFT-looking unpivoted LDL'
+// whose O(p^3) work is mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4), and every vector of the iteration lives in registers.
+//
+// Replaces, per problem: QPInteriorPointSolver::Setup + Solve (source/qp.cc:20-73, 100-151): ComputeInitialGuess
+// (:439-482), the Iterate loop (:153-201), EvaluateKKTConditions (:391-420), ComputeLDLT (:275-316) + SolveForUpdate
+// (:318-364) as ONE factorization and ONE two-sided solve, ComputeAlpha (:485-507), ComputeMu (:509-516),
+// ComputeErrors (:423-437).
+//
+// Why a second DMMA kernel next to qp_dm_kernel (CTA per problem, matrix in accumulator registers AND L in shared
+// memory): one factorization is a chain of p dependent pivots (~150-200 cycles each), so a CTA-per-problem kernel is
+// bound by that latency times the number of co-resident problems, and two on-chip copies of the matrix cap residency
+// at 4 problems per SM (n = 64). Here a problem costs one warp and ONE copy of the matrix (33 KB at n = 64, 10 KB at
+// n = 32): 6 resp. 18+ independent problems per SM, no CTA barriers, and the pivot chains of different problems
+// overlap.
+//
+// Layout: tile (I, J), I >= J, 64 doubles, element [r][c] at (c >> 2) * 32 + r * 4 + (c & 3): lane l = 4 r + q of a
+// warp reads [r][4h + q] at h * 32 + l -- which is at once the DMMA A fragment of the tile and the B fragment of its
+// transpose, 256 contiguous bytes, bank-conflict free. Tile row NT (one past the matrix) carries the right-hand side
+// in its row 0, so the forward substitution and the D^-1 scaling fall out of the panel solve.
+#pragma once
+#include "qp_dmma.cuh"
+
+namespace mo {
+
+template <int N, int K>
+struct WdLayout {
+  static constexpr int P = N + K, NT = P / 8, NTN = N / 8, NTR = NT + 1, M = 2 * N;
+  static constexpr int VPL = (N + 31) / 32;  // variables per lane
+  static_assert(N % 8 == 0 && K % 8 == 0 && N > 0 && K > 0 && K <= 32, "tile shapes");
+  __host__ __device__ static constexpr int colbase(int J) { return J * NTR - J * (J - 1) / 2; }
+  __host__ __device__ static constexpr int tile(int I, int J) { return 64 * (colbase(J) + (I - J)); }
+  static constexpr int NTILES = colbase(NT);
+  static constexpr int O_D = 64 * NTILES;   // pivots d[P]
+  static constexpr int O_INVD = O_D + P;    // 1 / d
+  static constexpr int O_XV = O_INVD + P;   // [x; -y] for the matvec, then the solution [dx; -dy]
+  static constexpr int O_R = O_XV + P;      // K [x; -y]
+  static constexpr int O_LS = O_R + P;      // 8x8 unit lower L_JJ (row-major) of the block being inverted
+  static constexpr int TOTAL = O_LS + 64;
+  static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
+};
+
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+  const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gsrc) : "memory");
+}
+
+__device__ __forceinline__ double wd_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double wd_min(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// sum over the 8 lanes that share q = lane & 3 (lanes differ in r = lane >> 2)
+__device__ __forceinline__ double wd_sum_r(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  return v;
+}
+
+// cp.async staging of G (lower block triangle) and A_eq into the tiles; every request is 8 rows x 4 columns:
+// four 64-byte column segments in global memory, 256 contiguous bytes in shared memory.
+template <int N, int K>
+__device__ __forceinline__ void wd_stage(double* __restrict__ T, const double* __restrict__ Gp,
+                                         const double* __restrict__ Ap, int lane) {
+  using L = WdLayout<N, K>;
+  const int r = lane >> 2, q = lane & 3;
+  const double* __restrict__ g = Gp + q * N + r;
+  const double* __restrict__ a = Ap + q * K + r;
+#pragma unroll
+  for (int J = 0; J < L::NTN; ++J) {
+#pragma unroll
+    for (int I = J; I < L::NTN; ++I) {
+      cp_async8(T + L::tile(I, J) + lane, g + (8 * J) * N + 8 * I);
+      cp_async8(T + L::tile(I, J) + 32 + lane, g + (8 * J + 4) * N + 8 * I);
+    }
+#pragma unroll
+    for (int I = L::NTN; I < L::NT; ++I) {
+      cp_async8(T + L::tile(I, J) + lane, a + (8 * J) * K + 8 * (I - L::NTN));
+      cp_async8(T + L::tile(I, J) + 32 + lane, a + (8 * J + 4) * K + 8 * (I - L::NTN));
+    }
+  }
+  cp_async_commit();
+}
+
+// LDL' of the 8x8 diagonal block stored in `tile` (lower triangle significant): lane & 7 = row, pivots in PAIRS
+// (1/d1 = a00 / det) so that the two reciprocal chains of a pair overlap. Writes d, 1/d and OVERWRITES the tile with
+// S = inv(L_JJ) (unit lower; the panel solve and the back substitution only ever need the inverse). `chk` turns NaN
+// on a zero or non-finite pivot.
+__device__ __noinline__ void wd_diag_block(double* __restrict__ tile, double* __restrict__ d, double* __restrict__ invd,
+                                           double* __restrict__ ls, double& chk_io) {
+  const int lane = threadIdx.x & 31, lr = lane & 7;
+  double a[8];
+  {
+    const double2 v0 = *reinterpret_cast<const double2*>(tile + lr * 4);
+    const double2 v1 = *reinterpret_cast<const double2*>(tile + lr * 4 + 2);
+    const double2 v2 = *reinterpret_cast<const double2*>(tile + 32 + lr * 4);
+    const double2 v3 = *reinterpret_cast<const double2*>(tile + 32 + lr * 4 + 2);
+    a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y; a[6] = v3.x; a[7] = v3.y;
+  }
+  double chk = chk_io, myd = 0.0, myinv = 0.0;
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    const double a00 = __shfl_sync(0xffffffffu, a[c], c);
+    const double a10 = __shfl_sync(0xffffffffu, a[c], c + 1);
+    const double a11 = __shfl_sync(0xffffffffu, a[c + 1], c + 1);
+    const double det = fma(a00, a11, -(a10 * a10));
+    const double inv0 = rcp_chain(a00), rdet = rcp_chain(det);
+    const double inv1 = a00 * rdet;  // 1 / d1, d1 = det / a00
+    const double d1 = fma(-(a10 * inv0), a10, a11);
+    chk = fma(inv0, 0.0, chk);
+    chk = fma(inv1, 0.0, chk);
+    const double u0 = a[c], l0 = u0 * inv0;
+    const double u1 = fma(-l0, a10, a[c + 1]), l1 = u1 * inv1;
+#pragma unroll
+    for (int c2 = c + 2; c2 < 8; ++c2) {
+      const double v0 = __shfl_sync(0xffffffffu, u0, c2), v1 = __shfl_sync(0xffffffffu, u1, c2);
+      a[c2] = fma(-l1, v1, fma(-l0, v0, a[c2]));
+    }
+    myd = lr == c ? a00 : (lr == c + 1 ? d1 : myd);
+    myinv = lr == c ? inv0 : (lr == c + 1 ? inv1 : myinv);
+    if (lane < 8) *reinterpret_cast<double2*>(ls + lr * 8 + c) = make_double2(l0, l1);  // entries right of the diagonal unused
+  }
+  if (lane < 8) { d[lr] = myd; invd[lr] = myinv; }
+  chk_io = chk;
+  __syncwarp();
+  // column lr of inv(L): x_i = e_i - sum_{k < i} L(i,k) x_k (x_i = 0 above the diagonal, 1 on it)
+  double x[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    double v = i == lr ? 1.0 : 0.0;
+#pragma unroll
+    for (int k = 0; k < i; ++k) v = fma(-ls[i * 8 + k], x[k], v);
+    x[i] = i >= lr ? v : 0.0;
+  }
+  if (lane < 8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) tile[(lr >> 2) * 32 + i * 4 + (lr & 3)] = x[i];  // S[i][lr]
+  }
+  __syncwarp();
+}
+
+// Block column J of the left-looking factorization: gather the updates of all earlier panels into the accumulator
+// fragments of tiles (J..NT, J), factor the diagonal block, solve the panel (and the right-hand-side row) with DMMA
+// against T = inv(L_JJ)' D_J^-1.
+template <int N, int K, int J>
+__device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, double& chk) {
+  using L = WdLayout<N, K>;
+  constexpr int CNT = L::NTR - J;
+  double* __restrict__ T = sm;
+  const int r = lane >> 2, q = lane & 3;
+  const int coff = (q >> 1) * 32 + r * 4 + 2 * (q & 1);  // accumulator fragment: [r][2q], [r][2q+1]
+  double acc[CNT][2];
+#pragma unroll
+  for (int i = 0; i < CNT; ++i) {
+    const double2 v = *reinterpret_cast<const double2*>(T + L::tile(J + i, J) + coff);
+    acc[i][0] = v.x; acc[i][1] = v.y;
+  }
+  if constexpr (J > 0) {
+#pragma unroll 1
+    for (int kk = 0; kk < J; ++kk) {
+      const double* __restrict__ tb = T + 64 * (kk * L::NTR - (kk * (kk - 1)) / 2 + (J - kk));  // tile (J, kk)
+      const double b0 = tb[lane] * -sm[L::O_D + 8 * kk + q];
+      const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * kk + 4 + q];
+      double a0[CNT], a1[CNT];
+#pragma unroll
+      for (int i = 0; i < CNT; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
+#pragma unroll
+      for (int i = 0; i < CNT; ++i) dmma884(acc[i][0], acc[i][1], a0[i], b0);
+#pragma unroll
+      for (int i = 0; i < CNT; ++i) dmma884(acc[i][0], acc[i][1], a1[i], b1);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < CNT; ++i)
+    *reinterpret_cast<double2*>(T + L::tile(J + i, J) + coff) = make_double2(acc[i][0], acc[i][1]);
+  __syncwarp();
+  wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, sm + L::O_LS, chk);
+  const double idr = sm[L::O_INVD + 8 * J + r];
+  const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
+  double a0[CNT], a1[CNT];
+#pragma unroll
+  for (int i = 1; i < CNT; ++i) { a0[i] = T[L::tile(J + i, J) + lane]; a1[i] = T[L::tile(J + i, J) + 32 + lane]; }
+  __syncwarp();
+#pragma unroll
+  for (int i = 1; i < CNT; ++i) {
+    double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0;
+    dmma884(p0, p1, a0[i], bt0);
+    dmma884(q0, q1, a1[i], bt1);
+    *reinterpret_cast<double2*>(T + L::tile(J + i, J) + coff) = make_double2(p0 + q0, p1 + q1);
+  }
+  __syncwarp();
+}
+
+template <int N, int K, int J>
+__device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, double& chk) {
+  if constexpr (J < WdLayout<N, K>::NT) {
+    wd_column<N, K, J>(sm, lane, chk);
+    wd_columns<N, K, J + 1>(sm, lane, chk);
+  }
+}
+
+// Factor the KKT matrix held in the tiles and solve for the right-hand side held in row 0 of tile row NT.
+// On return sm[O_XV .. O_XV + P) = K^-1 rhs. Returns false (uniformly) on a zero or non-finite pivot
+// (-> MO_QP_FAILED_FACTORIZATION, the batched stand-in for the exception of qp.cc:303-307).
+template <int N, int K>
+__device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane) {
+  using L = WdLayout<N, K>;
+  double chk = 0.0;
+  wd_columns<N, K, 0>(sm, lane, chk);
+  // back substitution L' x = w, w = D^-1 L^-1 rhs = row 0 of tile row NT; block J: t = w_J - sum_{I > J} L(I,J)' x_I,
+  // x_J = inv(L_JJ)' t with S = inv(L_JJ) stored in the diagonal tile.
+  const double* __restrict__ T = sm;
+  double* __restrict__ XS = sm + L::O_XV;
+  const int r = lane >> 2, q = lane & 3;
+#pragma unroll 1
+  for (int J = L::NT - 1; J >= 0; --J) {
+    const double* __restrict__ tj = T + 64 * (J * L::NTR - (J * (J - 1)) / 2);  // tile (J, J); tile (I, J) = tj + 64 (I - J)
+    double s0 = 0.0, s1 = 0.0;
+    for (int I = J + 1; I < L::NT; ++I) {
+      const double xr = XS[8 * I + r];
+      s0 = fma(tj[64 * (I - J) + lane], xr, s0);
+      s1 = fma(tj[64 * (I - J) + 32 + lane], xr, s1);
+    }
+    s0 = wd_sum_r(s0); s1 = wd_sum_r(s1);
+    const double* __restrict__ w = tj + 64 * (L::NT - J);
+    const double t0 = w[q] - s0, t1 = w[32 + q] - s1;  // t[q], t[4 + q] (replicated over r)
+    const double ta = __shfl_sync(0xffffffffu, t0, r & 3), tb = __shfl_sync(0xffffffffu, t1, r & 3);
+    const double tr = r >= 4 ? tb : ta;                // t[r]
+    double x0 = tj[lane] * tr, x1 = tj[32 + lane] * tr;  // S[r][4h + q] t[r]
+    x0 = wd_sum_r(x0); x1 = wd_sum_r(x1);
+    if (r == 0) { XS[8 * J + q] = x0; XS[8 * J + 4 + q] = x1; }
+    __syncwarp();
+  }
+  return chk == chk;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// The solve kernel: persistent single-warp CTAs, one problem per warp at a time. Lane l carries variables
+// v = l + 32 i (x, both slacks / multipliers / bounds, c) and equality row l (y, b_eq).
+// ---------------------------------------------------------------------------------------------------------
+template <int N, int K, int MINB>
+__global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
+  using L = WdLayout<N, K>;
+  constexpr int P = L::P, M = L::M, NT = L::NT, NTN = L::NTN, VPL = L::VPL, STRIDE = N + 2 * M + K;
+  extern __shared__ __align__(16) double sm[];
+  const int lane = threadIdx.x, r = lane >> 2, q = lane & 3;
+  double* __restrict__ T = sm;
+  double* __restrict__ XV = sm + L::O_XV;
+  double* __restrict__ R = sm + L::O_R;
+  const double tol2 = a.kkt_tol * a.kkt_tol, tau = 0.995;  // qp.cc:192
+  const bool isy = lane < K;
+
+  for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
+    const double* __restrict__ Gp = a.G + prob * (N * N);
+    const double* __restrict__ Ap = a.A + prob * (N * K);
+    double* __restrict__ vp = a.vars + prob * STRIDE;
+    __syncwarp();
+    wd_stage<N, K>(T, Gp, Ap, lane);
+    // right-hand-side tile row: rows 1..7 stay zero for the life of the problem
+#pragma unroll
+    for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + lane] = 0.0; }
+    double x[VPL], s0[VPL], s1[VPL], z0[VPL], z1[VPL], b0[VPL], b1[VPL], cv[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int v = lane + 32 * i;
+      x[i] = 0.0; s0[i] = s1[i] = z0[i] = z1[i] = 1.0; b0[i] = b1[i] = 1.0; cv[i] = 0.0;
+      if (v < N) {
+        cv[i] = a.c[prob * N + v];
+        const double2 bb = *reinterpret_cast<const double2*>(a.ib + prob * M + 2 * v);
+        b0[i] = bb.x; b1[i] = bb.y;
+      }
+    }
+    double y = 0.0;
+    const double be = isy ? a.b[prob * K + lane] : 0.0;
+    int status = -1, iters = 0;
+    // ComputeInitialGuess tail for my variables (qp.cc:462-481): clamp in list order (ClampX, qp.hpp:43-53),
+    // s = max(1e-9, a x + b), z = 1/s.
+    auto clamp_init = [&]() {
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        double xv = x[i];
+        xv = xv > -b0[i] ? xv : -b0[i];
+        xv = xv < b1[i] ? xv : b1[i];
+        x[i] = xv;
+        s0[i] = fmax(1.0e-9, xv + b0[i]); s1[i] = fmax(1.0e-9, b1[i] - xv);
+        z0[i] = 1.0 / s0[i]; z1[i] = 1.0 / s1[i];
+      }
+    };
+    bool guess_pending = a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;
+    if (a.guess == MO_GUESS_USER_PROVIDED) {
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        const int v = lane + 32 * i;
+        if (v < N) {
+          x[i] = vp[v];
+          s0[i] = vp[N + 2 * v]; s1[i] = vp[N + 2 * v + 1];
+          z0[i] = vp[N + M + K + 2 * v]; z1[i] = vp[N + M + K + 2 * v + 1];
+        }
+      }
+      if (isy) y = vp[N + M + lane];
+    } else if (!guess_pending) {
+      clamp_init();
+    }
+    double mu = a.initial_mu, alpha_p = 1.0, alpha_d = 1.0;
+    double kkt[4] = {0.0, 0.0, 0.0, 0.0};
+    bool first = true;
+    // ---- Solve loop (qp.cc:110-149); each trip = residuals of the current state, bookkeeping, one Newton step ----
+    while (status < 0) {
+      double rhsv[VPL], rhse = 0.0, p0[VPL], p1[VPL], w0[VPL], w1[VPL], i0[VPL], i1[VPL];
+      // publish [x; -y] for the matvec
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) XV[lane + 32 * i] = x[i];
+      if (isy) XV[N + lane] = -y;
+      cp_async_wait_all();
+      __syncwarp();
+      // the K x K zero block (the factorization overwrote it)
+#pragma unroll
+      for (int J = NTN; J < NT; ++J)
+#pragma unroll
+        for (int I = J; I < NT; ++I) { T[L::tile(I, J) + lane] = 0.0; T[L::tile(I, J) + 32 + lane] = 0.0; }
+      if (guess_pending) {  // KKT system without Sigma, rhs = -[c; b_eq]
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) rhsv[i] = -cv[i];
+        rhse = -be;
+      } else {
+        // (1) EvaluateKKTConditions (qp.cc:391-420): symmetric matvec [[G, A'],[A, 0]] [x; -y] over the stored tiles
+        double colacc[NTN][2];
+#pragma unroll
+        for (int J = 0; J < NTN; ++J) colacc[J][0] = colacc[J][1] = 0.0;
+#pragma unroll
+        for (int I = 0; I < NT; ++I) {
+          double ra = 0.0, rb = 0.0;
+          const double vr = XV[8 * I + r];
+#pragma unroll
+          for (int J = 0; J <= (I < NTN ? I : NTN - 1); ++J) {
+            const double e0 = T[L::tile(I, J) + lane], e1 = T[L::tile(I, J) + 32 + lane];  // [r][q], [r][4 + q]
+            const double v0 = XV[8 * J + q], v1 = XV[8 * J + 4 + q];
+            if (I == J) {  // diagonal tile: lower triangle significant
+              ra = q <= r ? fma(e0, v0, ra) : ra;
+              rb = 4 + q <= r ? fma(e1, v1, rb) : rb;
+              colacc[J][0] = q < r ? fma(e0, vr, colacc[J][0]) : colacc[J][0];
+              colacc[J][1] = 4 + q < r ? fma(e1, vr, colacc[J][1]) : colacc[J][1];
+            } else {
+              ra = fma(e0, v0, ra); rb = fma(e1, v1, rb);
+              colacc[J][0] = fma(e0, vr, colacc[J][0]);
+              colacc[J][1] = fma(e1, vr, colacc[J][1]);
+            }
+          }
+          double rs = ra + rb;
+          rs += __shfl_xor_sync(0xffffffffu, rs, 1);
+          rs += __shfl_xor_sync(0xffffffffu, rs, 2);
+          if (q == 0) R[8 * I + r] = rs;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int J = 0; J < NTN; ++J) {
+          const double c0 = wd_sum_r(colacc[J][0]), c1 = wd_sum_r(colacc[J][1]);
+          if (r == 0) { R[8 * J + q] += c0; R[8 * J + 4 + q] += c1; }
+        }
+        __syncwarp();
+        // (2) per-variable residuals, Sigma, r_aug pieces; norms (ComputeErrors, qp.cc:423-437)
+        double red[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // |r_d|^2, |r_pe|^2, |r_pi|^2, sum (sz)^2, sum sz, #(s <= 0)
+        double t1[VPL], t2[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+          const int v = lane + 32 * i;
+          t1[i] = t2[i] = p0[i] = p1[i] = w0[i] = w1[i] = i0[i] = i1[i] = 0.0;
+          if (v < N) {
+            const double base = R[v] + cv[i];
+            p0[i] = (x[i] + b0[i]) - s0[i]; p1[i] = (b1[i] - x[i]) - s1[i];
+            i0[i] = fast_rcp(s0[i]); i1[i] = fast_rcp(s1[i]);
+            w0[i] = z0[i] * i0[i]; w1[i] = z1[i] * i1[i];
+            const double rdv = (base - z0[i]) + z1[i];
+            const double c0 = s0[i] * z0[i], c1 = s1[i] * z1[i];
+            red[0] += rdv * rdv;
+            red[2] += fma(p0[i], p0[i], p1[i] * p1[i]);
+            red[3] += fma(c0, c0, c1 * c1);
+            red[4] += c0 + c1;
+            red[5] += ((s0[i] > 0.0) ? 0.0 : 1.0) + ((s1[i] > 0.0) ? 0.0 : 1.0);
+            t1[i] = base + fma(w0[i], p0[i], -(w1[i] * p1[i]));  // r_aug without the mu term (qp.cc:337-342)
+            t2[i] = i0[i] - i1[i];
+          }
+        }
+        double pe = 0.0;
+        if (isy) { pe = R[N + lane] + be; red[1] = pe * pe; }
+#pragma unroll
+        for (int i = 0; i < 6; ++i) red[i] = wd_sum(red[i]);
+        // (3) bookkeeping of the Solve loop: errors of the step just taken, termination, barrier update
+        const double mu_c = red[4] / (double)M;  // ComputeMu, qp.cc:509-516
+        const double corrected = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
+        const double comp2 = corrected > 0.0 ? corrected : 0.0;
+        if (first) {
+          first = false;
+          mu = a.init_mu_with_comp ? mu_c : a.initial_mu;
+        } else {
+          const double max2 = fmax(fmax(red[0], comp2), fmax(red[1], red[2]));
+          kkt[0] = sqrt(red[0]); kkt[1] = sqrt(comp2); kkt[2] = sqrt(red[1]); kkt[3] = sqrt(red[2]);
+          if (a.iter_log && lane == 0) {
+            double* row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+            row[4] = kkt[0]; row[5] = kkt[1]; row[6] = kkt[2]; row[7] = kkt[3];
+            row[8] = mu; row[9] = alpha_p; row[10] = alpha_d; row[11] = qnan(); row[12] = qnan(); row[13] = qnan();
+          }
+          ++iters;
+          if (max2 < tol2 && mu_c < a.comp_tol) status = MO_QP_SATISFIED_KKT_TOL;  // qp.cc:132-137
+          else if (iters >= a.max_iterations) status = MO_QP_MAX_ITERATIONS;
+          else if (max2 <= mu * mu || !a.decrease_mu_only_on_small_error)          // qp.cc:140-146
+            mu = (a.strategy == MO_BARRIER_FIXED_DECREASE) ? mu * a.sigma : a.sigma * mu_c;
+        }
+        if (status < 0 && red[5] != 0.0) status = MO_QP_NONPOSITIVE_SLACK;  // F_ASSERT(all s > 0), qp.cc:285
+        if (status >= 0) break;
+        if (a.iter_log && lane == 0) {  // kkt_initial of the coming iteration (ComputeErrors with the new mu, qp.cc:118)
+          double* row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+          const double cr = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
+          row[0] = sqrt(red[0]); row[1] = sqrt(cr > 0.0 ? cr : 0.0); row[2] = sqrt(red[1]); row[3] = sqrt(red[2]);
+        }
+        // (4) ComputeLDLT assembly (qp.cc:289-297): Sigma on the diagonal; rhs = -[r_aug; r_pe]
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+          const int v = lane + 32 * i;
+          rhsv[i] = -fma(-mu, t2[i], t1[i]);
+          if (v < N) {
+            const int jv = v >> 3, rr = v & 7;
+            T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2) + (rr >> 2) * 32 + rr * 4 + (rr & 3)] += w0[i] + w1[i];
+          }
+        }
+        rhse = -pe;
+      }
+      // right-hand side into row 0 of tile row NT
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        const int v = lane + 32 * i;
+        if (v < N) {
+          const int jv = v >> 3, cc = v & 7;
+          T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2 + (NT - jv)) + (cc >> 2) * 32 + (cc & 3)] = rhsv[i];
+        }
+      }
+      if (isy) {
+        const int e = N + lane, je = e >> 3, cc = e & 7;
+        T[64 * (je * L::NTR - (je * (je - 1)) / 2 + (NT - je)) + (cc >> 2) * 32 + (cc & 3)] = rhse;
+      }
+      __syncwarp();
+      const bool ok = wd_factor_solve<N, K>(sm, lane);
+      if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
+      wd_stage<N, K>(T, Gp, Ap, lane);  // next trip's G, A: overlaps the update below
+      if (guess_pending) {  // x <- dx, y <- dy of the equality constrained solve (qp.cc:452-459), then clamp / s / z
+        guess_pending = false;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) x[i] = XV[lane + 32 * i];
+        if (isy) y = -XV[N + lane];
+        clamp_init();
+        continue;
+      }
+      // (5) ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199)
+      double al0 = 1.0, al1 = 1.0, dx[VPL], d0[VPL], d1[VPL], e0[VPL], e1[VPL];
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        const int v = lane + 32 * i;
+        dx[i] = d0[i] = d1[i] = e0[i] = e1[i] = 0.0;
+        if (v < N) {
+          dx[i] = XV[v];
+          d0[i] = dx[i] + p0[i]; d1[i] = p1[i] - dx[i];
+          e0[i] = fma(mu, i0[i], -fma(w0[i], d0[i], z0[i]));
+          e1[i] = fma(mu, i1[i], -fma(w1[i], d1[i], z1[i]));
+          if (s0[i] + d0[i] <= 0.0 && fabs(d0[i]) > 0) al0 = fmin(al0, -tau * s0[i] / d0[i]);
+          if (s1[i] + d1[i] <= 0.0 && fabs(d1[i]) > 0) al0 = fmin(al0, -tau * s1[i] / d1[i]);
+          if (z0[i] + e0[i] <= 0.0 && fabs(e0[i]) > 0) al1 = fmin(al1, -tau * z0[i] / e0[i]);
+          if (z1[i] + e1[i] <= 0.0 && fabs(e1[i]) > 0) al1 = fmin(al1, -tau * z1[i] / e1[i]);
+        }
+      }
+      alpha_p = wd_min(al0); alpha_d = wd_min(al1);
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        x[i] = fma(dx[i], alpha_p, x[i]);
+        s0[i] = fma(d0[i], alpha_p, s0[i]); s1[i] = fma(d1[i], alpha_p, s1[i]);
+        z0[i] = fma(e0[i], alpha_d, z0[i]); z1[i] = fma(e1[i], alpha_d, z1[i]);
+      }
+      if (isy) y = fma(-XV[N + lane], alpha_d, y);
+    }
+    // ---- results ----
+    cp_async_wait_all();
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int v = lane + 32 * i;
+      if (v < N) {
+        vp[v] = x[i];
+        *reinterpret_cast<double2*>(vp + N + 2 * v) = make_double2(s0[i], s1[i]);
+        *reinterpret_cast<double2*>(vp + N + M + K + 2 * v) = make_double2(z0[i], z1[i]);
+      }
+    }
+    if (isy) vp[N + M + lane] = y;
+    if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
+      const double mn = wd_min(isy ? y : 1.0e300), li = -wd_min(isy ? -fabs(y) : 0.0);
+      if (lane == 0) { a.lagrange[prob * 2] = mn; a.lagrange[prob * 2 + 1] = li; }
+    }
+    if (lane == 0) {
+      a.status[prob] = status;
+      a.iters[prob] = iters;
+      if (a.kkt_final) {
+        double* kf = a.kkt_final + prob * 4;
+        kf[0] = kkt[0]; kf[1] = kkt[1]; kf[2] = kkt[2]; kf[3] = kkt[3];
+      }
+    }
+  }
+}
+
+}  // namespace mo
