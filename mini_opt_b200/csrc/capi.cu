@@ -9,7 +9,7 @@
 #include <vector>
 
 #include "qp_dmma.cuh"
-#include "qp_wdm.cuh"
+#include "wd_launch.h"
 #include "qp_generic.cuh"
 #include "qp_tpp.cuh"
 
@@ -199,30 +199,6 @@ int launch_dm(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
   return MO_OK;
 }
 
-// (N, K, min CTAs per SM) shapes of the warp-per-problem DMMA kernel (qp_wdm.cuh); same eligibility as the CTA kernel.
-#define MO_WD_SHAPES(X) X(64, 16, 6) X(32, 8, 16) X(16, 8, 24)
-
-template <int N, int K, int MINB>
-int launch_wd(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
-  using L = mo::WdLayout<N, K>;
-  auto kernel = mo::qp_wd_kernel<N, K, MINB>;
-  static thread_local int configured_dev = -1;
-  static thread_local int bps = 0;
-  int cur = 0;
-  MO_CUDA(cudaGetDevice(&cur));
-  if (configured_dev != cur) {
-    MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
-    MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32, L::SMEM_BYTES));
-    if (bps < 1) { g_last_error = "wd kernel does not fit on an SM"; return MO_ERR_UNSUPPORTED_SHAPE; }
-    configured_dev = cur;
-  }
-  const long long cap = (long long)dev.sms * bps;
-  kernel<<<(int)(a.batch < cap ? a.batch : cap), 32, L::SMEM_BYTES, stream>>>(a);
-  g_launches.fetch_add(1);
-  MO_CUDA(cudaGetLastError());
-  return MO_OK;
-}
-
 // MO_QP_DM_KERNEL=cta selects the CTA-per-problem kernel (qp_dmma.cuh) for A/B runs; default: warp per problem.
 bool dm_use_cta_kernel() {
   const char* e = getenv("MO_QP_DM_KERNEL");
@@ -289,9 +265,11 @@ int dispatch_solve(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stre
 #undef X
   }
   if (vec_ok && dm_eligible(a.n, a.k, a.m, a.flags, a.icount != nullptr, a.strategy) && !dm_use_cta_kernel()) {
-#define X(N_, K_, B_) if (a.n == N_ && a.k == K_) return launch_wd<N_, K_, B_>(a, dev, stream);
-    MO_WD_SHAPES(X)
-#undef X
+    if (mo::wd_has_shape(a.n, a.k)) {
+      MO_CUDA(mo::wd_launch(a, dev.sms, stream));
+      g_launches.fetch_add(1);
+      return MO_OK;
+    }
   }
   if (vec_ok && dm_eligible(a.n, a.k, a.m, a.flags, a.icount != nullptr, a.strategy)) {
 #define X(N_, K_, W_, B_) if (a.n == N_ && a.k == K_) return launch_dm<N_, K_, W_, B_>(a, dev, stream);

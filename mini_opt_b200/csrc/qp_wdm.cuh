@@ -19,6 +19,7 @@
 // transpose, 256 contiguous bytes, bank-conflict free. Tile row NT (one past the matrix) carries the right-hand side
 // in its row 0, so the forward substitution and the D^-1 scaling fall out of the panel solve.
 #pragma once
+#include <cstdio>
 #include "qp_dmma.cuh"
 
 namespace mo {
@@ -39,6 +40,15 @@ struct WdLayout {
   static constexpr int TOTAL = O_LS + 64;
   static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
 };
+
+#ifdef MO_WD_TRACE
+// Debug build only: lane 0 of CTA 0 accumulates cycles per phase in shared memory and prints them at kernel end.
+__shared__ long long s_wd_tr[16];
+__shared__ long long s_wd_t0;
+#define WD_T(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long t_ = clock64(); s_wd_tr[i] += t_ - s_wd_t0; s_wd_t0 = t_; } } while (0)
+#else
+#define WD_T(i) do {} while (0)
+#endif
 
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
   const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
@@ -88,57 +98,74 @@ __device__ __forceinline__ void wd_stage(double* __restrict__ T, const double* _
   cp_async_commit();
 }
 
-// LDL' of the 8x8 diagonal block stored in `tile` (lower triangle significant): lane & 7 = row, pivots in PAIRS
-// (1/d1 = a00 / det) so that the two reciprocal chains of a pair overlap. Writes d, 1/d and OVERWRITES the tile with
-// S = inv(L_JJ) (unit lower; the panel solve and the back substitution only ever need the inverse). `chk` turns NaN
-// on a zero or non-finite pivot.
+// LDL' of the 8x8 diagonal block stored in `tile` (lower triangle significant), computed REDUNDANTLY by every lane
+// from a register copy of the block: no shuffles and no selects on the pivot chain, which is the critical path of the
+// whole factorization (a lane-per-row version with shuffles measured 1460 cycles per block, its inverse 640). Pivots in
+// PAIRS (1/d1 = a00 / det, the multiplication folded into the last step of the reciprocal) so that the two reciprocal
+// chains of a pair overlap; the entries that feed the NEXT pair are updated with a single operation after 1/d1
+// arrives. Writes d, 1/d and OVERWRITES the tile with S = inv(L_JJ) (unit lower; the panel solve and the back
+// substitution only ever need the inverse): lane c < 8 computes column c of S from the register copy of L.
+// `chk` turns NaN on a zero or non-finite pivot.
 __device__ __noinline__ void wd_diag_block(double* __restrict__ tile, double* __restrict__ d, double* __restrict__ invd,
-                                           double* __restrict__ ls, double& chk_io) {
+                                           double& chk_io) {
   const int lane = threadIdx.x & 31, lr = lane & 7;
-  double a[8];
-  {
-    const double2 v0 = *reinterpret_cast<const double2*>(tile + lr * 4);
-    const double2 v1 = *reinterpret_cast<const double2*>(tile + lr * 4 + 2);
-    const double2 v2 = *reinterpret_cast<const double2*>(tile + 32 + lr * 4);
-    const double2 v3 = *reinterpret_cast<const double2*>(tile + 32 + lr * 4 + 2);
-    a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y; a[6] = v3.x; a[7] = v3.y;
+  double A[8][8];  // lower triangle; after the factorization the strict lower triangle holds L
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+#pragma unroll
+    for (int j = 0; j <= i; j += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(tile + (j >> 2) * 32 + i * 4 + (j & 3));
+      A[i][j] = v.x;
+      if (j + 1 <= i) A[i][j + 1] = v.y;
+    }
   }
-  double chk = chk_io, myd = 0.0, myinv = 0.0;
+  double chk = chk_io, dd[8], di[8];
 #pragma unroll
   for (int c = 0; c < 8; c += 2) {
-    const double a00 = __shfl_sync(0xffffffffu, a[c], c);
-    const double a10 = __shfl_sync(0xffffffffu, a[c], c + 1);
-    const double a11 = __shfl_sync(0xffffffffu, a[c + 1], c + 1);
+    const double a00 = A[c][c], a10 = A[c + 1][c], a11 = A[c + 1][c + 1];
     const double det = fma(a00, a11, -(a10 * a10));
-    const double inv0 = rcp_chain(a00), rdet = rcp_chain(det);
-    const double inv1 = a00 * rdet;  // 1 / d1, d1 = det / a00
-    const double d1 = fma(-(a10 * inv0), a10, a11);
+    const double inv0 = rcp_chain(a00);
+    double xd;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(xd) : "d"(det));
+    const double ed = fma(-det, xd, 1.0), yd = a00 * xd;
+    const double inv1 = fma(yd, fma(ed, ed, ed), yd);  // 1 / d1, d1 = det / a00
+    dd[c] = a00; dd[c + 1] = fma(-(a10 * inv0), a10, a11);
+    di[c] = inv0; di[c + 1] = inv1;
     chk = fma(inv0, 0.0, chk);
     chk = fma(inv1, 0.0, chk);
-    const double u0 = a[c], l0 = u0 * inv0;
-    const double u1 = fma(-l0, a10, a[c + 1]), l1 = u1 * inv1;
+    A[c + 1][c] = a10 * inv0;
+    double u0[8], u1[8], l0[8];
 #pragma unroll
-    for (int c2 = c + 2; c2 < 8; ++c2) {
-      const double v0 = __shfl_sync(0xffffffffu, u0, c2), v1 = __shfl_sync(0xffffffffu, u1, c2);
-      a[c2] = fma(-l1, v1, fma(-l0, v0, a[c2]));
+    for (int i = c + 2; i < 8; ++i) {
+      u0[i] = A[i][c];
+      l0[i] = u0[i] * inv0;
+      u1[i] = fma(-l0[i], a10, A[i][c + 1]);
     }
-    myd = lr == c ? a00 : (lr == c + 1 ? d1 : myd);
-    myinv = lr == c ? inv0 : (lr == c + 1 ? inv1 : myinv);
-    if (lane < 8) *reinterpret_cast<double2*>(ls + lr * 8 + c) = make_double2(l0, l1);  // entries right of the diagonal unused
+#pragma unroll
+    for (int i = c + 2; i < 8; ++i) {
+#pragma unroll
+      for (int j = c + 2; j <= i; ++j)  // A(i,j) -= l0_i u0_j + (u1_i u1_j) / d1
+        A[i][j] = fma(-(u1[i] * u1[j]), inv1, fma(-l0[i], u0[j], A[i][j]));
+      A[i][c] = l0[i];
+      A[i][c + 1] = u1[i] * inv1;
+    }
   }
-  if (lane < 8) { d[lr] = myd; invd[lr] = myinv; }
   chk_io = chk;
-  __syncwarp();
   // column lr of inv(L): x_i = e_i - sum_{k < i} L(i,k) x_k (x_i = 0 above the diagonal, 1 on it)
   double x[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     double v = i == lr ? 1.0 : 0.0;
 #pragma unroll
-    for (int k = 0; k < i; ++k) v = fma(-ls[i * 8 + k], x[k], v);
+    for (int k = 0; k < i; ++k) v = fma(-A[i][k], x[k], v);
     x[i] = i >= lr ? v : 0.0;
   }
+  double myd = dd[0], myinv = di[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) { myd = lr == i ? dd[i] : myd; myinv = lr == i ? di[i] : myinv; }
+  __syncwarp();  // every lane has read the block
   if (lane < 8) {
+    d[lr] = myd; invd[lr] = myinv;
 #pragma unroll
     for (int i = 0; i < 8; ++i) tile[(lr >> 2) * 32 + i * 4 + (lr & 3)] = x[i];  // S[i][lr]
   }
@@ -162,9 +189,11 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
     acc[i][0] = v.x; acc[i][1] = v.y;
   }
   if constexpr (J > 0) {
-#pragma unroll 1
+    // fully unrolled: tile addresses are immediates and the scheduler hoists the fragment loads of panel kk+1 above
+    // the DMMAs of panel kk (a runtime loop spent more cycles on addressing and load latency than on DMMA)
+#pragma unroll
     for (int kk = 0; kk < J; ++kk) {
-      const double* __restrict__ tb = T + 64 * (kk * L::NTR - (kk * (kk - 1)) / 2 + (J - kk));  // tile (J, kk)
+      const double* __restrict__ tb = T + L::tile(J, kk);
       const double b0 = tb[lane] * -sm[L::O_D + 8 * kk + q];
       const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * kk + 4 + q];
       double a0[CNT], a1[CNT];
@@ -180,7 +209,9 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
   for (int i = 0; i < CNT; ++i)
     *reinterpret_cast<double2*>(T + L::tile(J + i, J) + coff) = make_double2(acc[i][0], acc[i][1]);
   __syncwarp();
-  wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, sm + L::O_LS, chk);
+  WD_T(2);
+  wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, chk);
+  WD_T(3);
   const double idr = sm[L::O_INVD + 8 * J + r];
   const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
   double a0[CNT], a1[CNT];
@@ -195,6 +226,7 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
     *reinterpret_cast<double2*>(T + L::tile(J + i, J) + coff) = make_double2(p0 + q0, p1 + q1);
   }
   __syncwarp();
+  WD_T(4);
 }
 
 template <int N, int K, int J>
@@ -212,6 +244,7 @@ template <int N, int K>
 __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane) {
   using L = WdLayout<N, K>;
   double chk = 0.0;
+  WD_T(1);
   wd_columns<N, K, 0>(sm, lane, chk);
   // back substitution L' x = w, w = D^-1 L^-1 rhs = row 0 of tile row NT; block J: t = w_J - sum_{I > J} L(I,J)' x_I,
   // x_J = inv(L_JJ)' t with S = inv(L_JJ) stored in the diagonal tile.
@@ -237,6 +270,7 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
     if (r == 0) { XS[8 * J + q] = x0; XS[8 * J + 4 + q] = x1; }
     __syncwarp();
   }
+  WD_T(5);
   return chk == chk;
 }
 
@@ -255,6 +289,10 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
   double* __restrict__ R = sm + L::O_R;
   const double tol2 = a.kkt_tol * a.kkt_tol, tau = 0.995;  // qp.cc:192
   const bool isy = lane < K;
+#ifdef MO_WD_TRACE
+  if (threadIdx.x == 0) { for (int i = 0; i < 16; ++i) s_wd_tr[i] = 0; s_wd_t0 = clock64(); }
+  __syncwarp();
+#endif
 
   for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
     const double* __restrict__ Gp = a.G + prob * (N * N);
@@ -364,6 +402,7 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
           if (r == 0) { R[8 * J + q] += c0; R[8 * J + 4 + q] += c1; }
         }
         __syncwarp();
+        WD_T(0);
         // (2) per-variable residuals, Sigma, r_aug pieces; norms (ComputeErrors, qp.cc:423-437)
         double red[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // |r_d|^2, |r_pe|^2, |r_pi|^2, sum (sz)^2, sum sz, #(s <= 0)
         double t1[VPL], t2[VPL];
@@ -448,6 +487,7 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
       const bool ok = wd_factor_solve<N, K>(sm, lane);
       if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
       wd_stage<N, K>(T, Gp, Ap, lane);  // next trip's G, A: overlaps the update below
+      WD_T(6);
       if (guess_pending) {  // x <- dx, y <- dy of the equality constrained solve (qp.cc:452-459), then clamp / s / z
         guess_pending = false;
 #pragma unroll
@@ -481,6 +521,7 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
         z0[i] = fma(e0[i], alpha_d, z0[i]); z1[i] = fma(e1[i], alpha_d, z1[i]);
       }
       if (isy) y = fma(-XV[N + lane], alpha_d, y);
+      WD_T(7);
     }
     // ---- results ----
     cp_async_wait_all();
@@ -506,7 +547,14 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
         kf[0] = kkt[0]; kf[1] = kkt[1]; kf[2] = kkt[2]; kf[3] = kkt[3];
       }
     }
+    WD_T(8);
   }
+#ifdef MO_WD_TRACE
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    printf("wd trace n=%d: matvec %lld | pervar+bookkeeping+rhs %lld | gather %lld | diag+inv %lld | panel %lld | backsub %lld | stage %lld | update %lld | results+load %lld\n",
+           N, s_wd_tr[0], s_wd_tr[1], s_wd_tr[2], s_wd_tr[3], s_wd_tr[4], s_wd_tr[5], s_wd_tr[6], s_wd_tr[7], s_wd_tr[8]);
+
+#endif
 }
 
 }  // namespace mo
