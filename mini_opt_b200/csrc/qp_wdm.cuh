@@ -28,6 +28,9 @@ template <int N, int K>
 struct WdLayout {
   static constexpr int P = N + K, NT = P / 8, NTN = N / 8, NTR = NT + 1, M = 2 * N;
   static constexpr int VPL = (N + 31) / 32;  // variables per lane
+  // stage the next trip's G, A column by column inside the back substitution (measured: n = 64 19.85 -> 19.53 ms;
+  // n = 32 / 16 slower, their loop is issue-bound) or in one piece after it
+  static constexpr bool STAGE_IN_BACKSUB = N >= 64;
   static_assert(N % 8 == 0 && K % 8 == 0 && N > 0 && K > 0 && K <= 32, "tile shapes");
   __host__ __device__ static constexpr int colbase(int J) { return J * NTR - J * (J - 1) / 2; }
   __host__ __device__ static constexpr int tile(int I, int J) { return 64 * (colbase(J) + (I - J)); }
@@ -36,8 +39,9 @@ struct WdLayout {
   static constexpr int O_INVD = O_D + P;    // 1 / d
   static constexpr int O_XV = O_INVD + P;   // [x; -y] for the matvec, then the solution [dx; -dy]
   static constexpr int O_R = O_XV + P;      // K [x; -y]
-  static constexpr int O_LS = O_R + P;      // 8x8 unit lower L_JJ (row-major) of the block being inverted
-  static constexpr int TOTAL = O_LS + 64;
+  static constexpr int O_RC = O_R + P;      // two-warp variant: the helper warp's column sums of the matvec [N]
+  static constexpr int O_CTL = O_RC + N;    // two-warp variant: status broadcast
+  static constexpr int TOTAL = O_CTL + 2;
   static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
 };
 
@@ -75,24 +79,29 @@ __device__ __forceinline__ double wd_sum_r(double v) {
 
 // cp.async staging of G (lower block triangle) and A_eq into the tiles; every request is 8 rows x 4 columns:
 // four 64-byte column segments in global memory, 256 contiguous bytes in shared memory.
-template <int N, int K>
+template <int N, int K, int NW>
 __device__ __forceinline__ void wd_stage(double* __restrict__ T, const double* __restrict__ Gp,
-                                         const double* __restrict__ Ap, int lane) {
+                                         const double* __restrict__ Ap, int lane, int warp) {
   using L = WdLayout<N, K>;
   const int r = lane >> 2, q = lane & 3;
   const double* __restrict__ g = Gp + q * N + r;
   const double* __restrict__ a = Ap + q * K + r;
+  int cnt = 0;  // the warps of a problem take alternate tiles
 #pragma unroll
   for (int J = 0; J < L::NTN; ++J) {
 #pragma unroll
-    for (int I = J; I < L::NTN; ++I) {
-      cp_async8(T + L::tile(I, J) + lane, g + (8 * J) * N + 8 * I);
-      cp_async8(T + L::tile(I, J) + 32 + lane, g + (8 * J + 4) * N + 8 * I);
+    for (int I = J; I < L::NTN; ++I, ++cnt) {
+      if (NW == 1 || (cnt % NW) == warp) {
+        cp_async8(T + L::tile(I, J) + lane, g + (8 * J) * N + 8 * I);
+        cp_async8(T + L::tile(I, J) + 32 + lane, g + (8 * J + 4) * N + 8 * I);
+      }
     }
 #pragma unroll
-    for (int I = L::NTN; I < L::NT; ++I) {
-      cp_async8(T + L::tile(I, J) + lane, a + (8 * J) * K + 8 * (I - L::NTN));
-      cp_async8(T + L::tile(I, J) + 32 + lane, a + (8 * J + 4) * K + 8 * (I - L::NTN));
+    for (int I = L::NTN; I < L::NT; ++I, ++cnt) {
+      if (NW == 1 || (cnt % NW) == warp) {
+        cp_async8(T + L::tile(I, J) + lane, a + (8 * J) * K + 8 * (I - L::NTN));
+        cp_async8(T + L::tile(I, J) + 32 + lane, a + (8 * J + 4) * K + 8 * (I - L::NTN));
+      }
     }
   }
   cp_async_commit();
@@ -229,23 +238,99 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
   WD_T(4);
 }
 
+// Two-warp variant of the block column step (look-ahead): warp 0 factors diagonal block J and solves panel J while
+// warp 1 gathers block column J+1 over the panels kk < J (independent of block J); after a barrier warp 1 applies the
+// kk = J update and spills column J+1. The pivot chain of block J and the DMMA gather of column J+1 overlap in
+// hardware instead of queueing in one in-order instruction stream.
 template <int N, int K, int J>
-__device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, double& chk) {
+__device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, int warp, double& chk) {
+  using L = WdLayout<N, K>;
+  constexpr int CP = L::NTR - J - 1;      // tiles below the diagonal block: I = J+1 .. NT (= the tiles of column J+1)
+  constexpr bool HASN = J + 1 < L::NT;    // a block column J+1 exists
+  double* __restrict__ T = sm;
+  const int r = lane >> 2, q = lane & 3;
+  const int coff = (q >> 1) * 32 + r * 4 + 2 * (q & 1);
+  double acc[CP][2];
+  if (warp == 0) {
+    wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, chk);
+    const double idr = sm[L::O_INVD + 8 * J + r];
+    const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
+    double f0[CP], f1[CP];
+#pragma unroll
+    for (int i = 0; i < CP; ++i) { f0[i] = T[L::tile(J + 1 + i, J) + lane]; f1[i] = T[L::tile(J + 1 + i, J) + 32 + lane]; }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < CP; ++i) {
+      double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0;
+      dmma884(p0, p1, f0[i], bt0);
+      dmma884(q0, q1, f1[i], bt1);
+      *reinterpret_cast<double2*>(T + L::tile(J + 1 + i, J) + coff) = make_double2(p0 + q0, p1 + q1);
+    }
+  } else if constexpr (HASN) {
+#pragma unroll
+    for (int i = 0; i < CP; ++i) {
+      const double2 v = *reinterpret_cast<const double2*>(T + L::tile(J + 1 + i, J + 1) + coff);
+      acc[i][0] = v.x; acc[i][1] = v.y;
+    }
+#pragma unroll
+    for (int kk = 0; kk < J; ++kk) {
+      const double* __restrict__ tb = T + L::tile(J + 1, kk);
+      const double b0 = tb[lane] * -sm[L::O_D + 8 * kk + q];
+      const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * kk + 4 + q];
+      double a0[CP], a1[CP];
+#pragma unroll
+      for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
+#pragma unroll
+      for (int i = 0; i < CP; ++i) dmma884(acc[i][0], acc[i][1], a0[i], b0);
+#pragma unroll
+      for (int i = 0; i < CP; ++i) dmma884(acc[i][0], acc[i][1], a1[i], b1);
+    }
+  }
+  WD_T(3);
+  __syncthreads();
+  WD_T(2);
+  if constexpr (HASN) {
+    if (warp == 1) {
+      const double* __restrict__ tb = T + L::tile(J + 1, J);
+      const double b0 = tb[lane] * -sm[L::O_D + 8 * J + q];
+      const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * J + 4 + q];
+      double a0[CP], a1[CP];
+#pragma unroll
+      for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
+#pragma unroll
+      for (int i = 0; i < CP; ++i) {
+        double e0 = 0.0, e1 = 0.0;  // second k-half in its own accumulator: two independent DMMAs per tile
+        dmma884(acc[i][0], acc[i][1], a0[i], b0);
+        dmma884(e0, e1, a1[i], b1);
+        *reinterpret_cast<double2*>(T + L::tile(J + 1 + i, J + 1) + coff) = make_double2(acc[i][0] + e0, acc[i][1] + e1);
+      }
+    }
+    __syncthreads();
+    WD_T(4);
+  }
+}
+
+template <int N, int K, int NW, int J>
+__device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, int warp, double& chk) {
   if constexpr (J < WdLayout<N, K>::NT) {
-    wd_column<N, K, J>(sm, lane, chk);
-    wd_columns<N, K, J + 1>(sm, lane, chk);
+    if constexpr (NW == 1) wd_column<N, K, J>(sm, lane, chk);
+    else wd2_column<N, K, J>(sm, lane, warp, chk);
+    wd_columns<N, K, NW, J + 1>(sm, lane, warp, chk);
   }
 }
 
 // Factor the KKT matrix held in the tiles and solve for the right-hand side held in row 0 of tile row NT.
-// On return sm[O_XV .. O_XV + P) = K^-1 rhs. Returns false (uniformly) on a zero or non-finite pivot
-// (-> MO_QP_FAILED_FACTORIZATION, the batched stand-in for the exception of qp.cc:303-307).
-template <int N, int K>
-__device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane) {
+// On return sm[O_XV .. O_XV + P) = K^-1 rhs and the cp.async staging of G, A_eq for the next trip is in flight. Returns false on a zero or non-finite pivot (-> MO_QP_FAILED_FACTORIZATION,
+// the batched stand-in for the exception of qp.cc:303-307); with two warps only warp 0 holds the answer.
+template <int N, int K, int NW>
+__device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane, int warp,
+                                                const double* __restrict__ Gp, const double* __restrict__ Ap) {
   using L = WdLayout<N, K>;
+  constexpr bool kStageInBacksub = WdLayout<N, K>::STAGE_IN_BACKSUB;
   double chk = 0.0;
   WD_T(1);
-  wd_columns<N, K, 0>(sm, lane, chk);
+  wd_columns<N, K, NW, 0>(sm, lane, warp, chk);
+  if (NW == 2 && warp != 0) return true;
   // back substitution L' x = w, w = D^-1 L^-1 rhs = row 0 of tile row NT; block J: t = w_J - sum_{I > J} L(I,J)' x_I,
   // x_J = inv(L_JJ)' t with S = inv(L_JJ) stored in the diagonal tile.
   const double* __restrict__ T = sm;
@@ -254,68 +339,104 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
 #pragma unroll 1
   for (int J = L::NT - 1; J >= 0; --J) {
     const double* __restrict__ tj = T + 64 * (J * L::NTR - (J * (J - 1)) / 2);  // tile (J, J); tile (I, J) = tj + 64 (I - J)
-    double s0 = 0.0, s1 = 0.0;
-    for (int I = J + 1; I < L::NT; ++I) {
-      const double xr = XS[8 * I + r];
-      s0 = fma(tj[64 * (I - J) + lane], xr, s0);
-      s1 = fma(tj[64 * (I - J) + 32 + lane], xr, s1);
+    // t[r] = w[r] - sum_I sum_k L(I,J)[k][r] x_I[k]: the tiles are read TRANSPOSED (element [4h + q][r], two contiguous
+    // 128-byte runs per request in this layout), so the sum over k is two accumulators per lane plus a reduction over
+    // q (2 shuffle levels), and t lands where the second product needs it (lane group r) without a broadcast.
+    const int toff = (r >> 2) * 32 + q * 4 + (r & 3);
+    double sa = 0.0, sb = 0.0, sc = 0.0, sd = 0.0;
+    for (int I = J + 1; I < L::NT; I += 2) {
+      const double* __restrict__ ti = tj + 64 * (I - J);
+      sa = fma(ti[toff], XS[8 * I + q], sa);
+      sb = fma(ti[toff + 16], XS[8 * I + 4 + q], sb);
+      if (I + 1 < L::NT) {
+        sc = fma(ti[64 + toff], XS[8 * I + 8 + q], sc);
+        sd = fma(ti[64 + toff + 16], XS[8 * I + 12 + q], sd);
+      }
     }
-    s0 = wd_sum_r(s0); s1 = wd_sum_r(s1);
+    double sq = (sa + sb) + (sc + sd);
+    sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+    sq += __shfl_xor_sync(0xffffffffu, sq, 2);
     const double* __restrict__ w = tj + 64 * (L::NT - J);
-    const double t0 = w[q] - s0, t1 = w[32 + q] - s1;  // t[q], t[4 + q] (replicated over r)
-    const double ta = __shfl_sync(0xffffffffu, t0, r & 3), tb = __shfl_sync(0xffffffffu, t1, r & 3);
-    const double tr = r >= 4 ? tb : ta;                // t[r]
+    const double tr = w[(r >> 2) * 32 + (r & 3)] - sq;   // t[r] (replicated over q)
     double x0 = tj[lane] * tr, x1 = tj[32 + lane] * tr;  // S[r][4h + q] t[r]
     x0 = wd_sum_r(x0); x1 = wd_sum_r(x1);
     if (r == 0) { XS[8 * J + q] = x0; XS[8 * J + 4 + q] = x1; }
     __syncwarp();
+    // block column J of L is consumed: stage the next trip's G, A into it now, under the rest of the substitution
+    if (kStageInBacksub && J < L::NTN) {
+      double* __restrict__ dst = sm + 64 * (J * L::NTR - (J * (J - 1)) / 2) + lane;
+      const double* __restrict__ g = Gp + (q + 8 * J) * N + r + 8 * J;
+      for (int I = J; I < L::NTN; ++I, dst += 64, g += 8) {
+        cp_async8(dst, g);
+        cp_async8(dst + 32, g + 4 * N);
+      }
+      const double* __restrict__ ap = Ap + (q + 8 * J) * K + r;
+      for (int I = L::NTN; I < L::NT; ++I, dst += 64, ap += 8) {
+        cp_async8(dst, ap);
+        cp_async8(dst + 32, ap + 4 * K);
+      }
+    }
   }
+  if (kStageInBacksub) cp_async_commit();
   WD_T(5);
   return chk == chk;
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// The solve kernel: persistent single-warp CTAs, one problem per warp at a time. Lane l carries variables
-// v = l + 32 i (x, both slacks / multipliers / bounds, c) and equality row l (y, b_eq).
+// The solve kernel: persistent CTAs of NW warps, one problem per CTA at a time. NW = 1: everything in one warp.
+// NW = 2: warp 0 owns the iteration (vectors, bookkeeping, diagonal blocks, panel solves, back substitution), warp 1
+// is the look-ahead helper (gather of the next block column, half of the staging, the A_eq rows of the matvec).
+// Lane l of warp 0 carries variables v = l + 32 i (x, both slacks / multipliers / bounds, c) and equality row l.
 // ---------------------------------------------------------------------------------------------------------
-template <int N, int K, int MINB>
-__global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
+template <int NW>
+__device__ __forceinline__ void wd_bar() {
+  if (NW == 1) __syncwarp(); else __syncthreads();
+}
+
+template <int N, int K, int NW, int MINB>
+__global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
   using L = WdLayout<N, K>;
   constexpr int P = L::P, M = L::M, NT = L::NT, NTN = L::NTN, VPL = L::VPL, STRIDE = N + 2 * M + K;
+  static_assert(NW == 1 || NW == 2, "one or two warps per problem");
   extern __shared__ __align__(16) double sm[];
-  const int lane = threadIdx.x, r = lane >> 2, q = lane & 3;
+  const int lane = threadIdx.x & 31, warp = NW == 1 ? 0 : (int)(threadIdx.x >> 5), r = lane >> 2, q = lane & 3;
+  const bool main_warp = warp == 0, helper = warp == NW - 1;  // NW = 1: the one warp plays both roles
   double* __restrict__ T = sm;
   double* __restrict__ XV = sm + L::O_XV;
   double* __restrict__ R = sm + L::O_R;
+  double* __restrict__ RC = sm + L::O_RC;
+  volatile int* ctl = reinterpret_cast<volatile int*>(sm + L::O_CTL);
   const double tol2 = a.kkt_tol * a.kkt_tol, tau = 0.995;  // qp.cc:192
   const bool isy = lane < K;
 #ifdef MO_WD_TRACE
   if (threadIdx.x == 0) { for (int i = 0; i < 16; ++i) s_wd_tr[i] = 0; s_wd_t0 = clock64(); }
-  __syncwarp();
+  wd_bar<NW>();
 #endif
 
   for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
     const double* __restrict__ Gp = a.G + prob * (N * N);
     const double* __restrict__ Ap = a.A + prob * (N * K);
     double* __restrict__ vp = a.vars + prob * STRIDE;
-    __syncwarp();
-    wd_stage<N, K>(T, Gp, Ap, lane);
+    wd_bar<NW>();
+    wd_stage<N, K, NW>(T, Gp, Ap, lane, warp);
     // right-hand-side tile row: rows 1..7 stay zero for the life of the problem
+    if (helper) {
 #pragma unroll
-    for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + lane] = 0.0; }
+      for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + lane] = 0.0; }
+    }
     double x[VPL], s0[VPL], s1[VPL], z0[VPL], z1[VPL], b0[VPL], b1[VPL], cv[VPL];
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
       const int v = lane + 32 * i;
       x[i] = 0.0; s0[i] = s1[i] = z0[i] = z1[i] = 1.0; b0[i] = b1[i] = 1.0; cv[i] = 0.0;
-      if (v < N) {
+      if (v < N && main_warp) {
         cv[i] = a.c[prob * N + v];
         const double2 bb = *reinterpret_cast<const double2*>(a.ib + prob * M + 2 * v);
         b0[i] = bb.x; b1[i] = bb.y;
       }
     }
     double y = 0.0;
-    const double be = isy ? a.b[prob * K + lane] : 0.0;
+    const double be = (isy && main_warp) ? a.b[prob * K + lane] : 0.0;
     int status = -1, iters = 0;
     // ComputeInitialGuess tail for my variables (qp.cc:462-481): clamp in list order (ClampX, qp.hpp:43-53),
     // s = max(1e-9, a x + b), z = 1/s.
@@ -330,18 +451,20 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
         z0[i] = 1.0 / s0[i]; z1[i] = 1.0 / s1[i];
       }
     };
-    bool guess_pending = a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;
+    bool guess_pending = a.guess == MO_GUESS_SOLVE_EQUALITY_CONSTRAINED;  // uniform over the CTA
     if (a.guess == MO_GUESS_USER_PROVIDED) {
+      if (main_warp) {
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) {
-        const int v = lane + 32 * i;
-        if (v < N) {
-          x[i] = vp[v];
-          s0[i] = vp[N + 2 * v]; s1[i] = vp[N + 2 * v + 1];
-          z0[i] = vp[N + M + K + 2 * v]; z1[i] = vp[N + M + K + 2 * v + 1];
+        for (int i = 0; i < VPL; ++i) {
+          const int v = lane + 32 * i;
+          if (v < N) {
+            x[i] = vp[v];
+            s0[i] = vp[N + 2 * v]; s1[i] = vp[N + 2 * v + 1];
+            z0[i] = vp[N + M + K + 2 * v]; z1[i] = vp[N + M + K + 2 * v + 1];
+          }
         }
+        if (isy) y = vp[N + M + lane];
       }
-      if (isy) y = vp[N + M + lane];
     } else if (!guess_pending) {
       clamp_init();
     }
@@ -349,30 +472,36 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
     double kkt[4] = {0.0, 0.0, 0.0, 0.0};
     bool first = true;
     // ---- Solve loop (qp.cc:110-149); each trip = residuals of the current state, bookkeeping, one Newton step ----
-    while (status < 0) {
+    for (;;) {
       double rhsv[VPL], rhse = 0.0, p0[VPL], p1[VPL], w0[VPL], w1[VPL], i0[VPL], i1[VPL];
       // publish [x; -y] for the matvec
+      if (main_warp) {
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) XV[lane + 32 * i] = x[i];
-      if (isy) XV[N + lane] = -y;
+        for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) XV[lane + 32 * i] = x[i];
+        if (isy) XV[N + lane] = -y;
+      }
       cp_async_wait_all();
-      __syncwarp();
+      wd_bar<NW>();
       // the K x K zero block (the factorization overwrote it)
+      if (helper) {
 #pragma unroll
-      for (int J = NTN; J < NT; ++J)
+        for (int J = NTN; J < NT; ++J)
 #pragma unroll
-        for (int I = J; I < NT; ++I) { T[L::tile(I, J) + lane] = 0.0; T[L::tile(I, J) + 32 + lane] = 0.0; }
+          for (int I = J; I < NT; ++I) { T[L::tile(I, J) + lane] = 0.0; T[L::tile(I, J) + 32 + lane] = 0.0; }
+      }
       if (guess_pending) {  // KKT system without Sigma, rhs = -[c; b_eq]
 #pragma unroll
         for (int i = 0; i < VPL; ++i) rhsv[i] = -cv[i];
         rhse = -be;
       } else {
-        // (1) EvaluateKKTConditions (qp.cc:391-420): symmetric matvec [[G, A'],[A, 0]] [x; -y] over the stored tiles
+        // (1) EvaluateKKTConditions (qp.cc:391-420): symmetric matvec [[G, A'],[A, 0]] [x; -y] over the stored tiles;
+        //     the main warp takes the G tile rows, the helper the A_eq tile rows
         double colacc[NTN][2];
 #pragma unroll
         for (int J = 0; J < NTN; ++J) colacc[J][0] = colacc[J][1] = 0.0;
 #pragma unroll
         for (int I = 0; I < NT; ++I) {
+          if (I < NTN ? !main_warp : !helper) continue;
           double ra = 0.0, rb = 0.0;
           const double vr = XV[8 * I + r];
 #pragma unroll
@@ -399,10 +528,15 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
 #pragma unroll
         for (int J = 0; J < NTN; ++J) {
           const double c0 = wd_sum_r(colacc[J][0]), c1 = wd_sum_r(colacc[J][1]);
-          if (r == 0) { R[8 * J + q] += c0; R[8 * J + 4 + q] += c1; }
+          if (r == 0) {
+            if (NW == 1) { R[8 * J + q] += c0; R[8 * J + 4 + q] += c1; }
+            else if (main_warp) { R[8 * J + q] += c0; R[8 * J + 4 + q] += c1; }
+            else { RC[8 * J + q] = c0; RC[8 * J + 4 + q] = c1; }
+          }
         }
-        __syncwarp();
+        wd_bar<NW>();
         WD_T(0);
+        if (main_warp) {
         // (2) per-variable residuals, Sigma, r_aug pieces; norms (ComputeErrors, qp.cc:423-437)
         double red[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // |r_d|^2, |r_pe|^2, |r_pi|^2, sum (sz)^2, sum sz, #(s <= 0)
         double t1[VPL], t2[VPL];
@@ -411,7 +545,7 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
           const int v = lane + 32 * i;
           t1[i] = t2[i] = p0[i] = p1[i] = w0[i] = w1[i] = i0[i] = i1[i] = 0.0;
           if (v < N) {
-            const double base = R[v] + cv[i];
+            const double base = (NW == 1 ? R[v] : R[v] + RC[v]) + cv[i];
             p0[i] = (x[i] + b0[i]) - s0[i]; p1[i] = (b1[i] - x[i]) - s1[i];
             i0[i] = fast_rcp(s0[i]); i1[i] = fast_rcp(s1[i]);
             w0[i] = z0[i] * i0[i]; w1[i] = z1[i] * i1[i];
@@ -452,50 +586,70 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
             mu = (a.strategy == MO_BARRIER_FIXED_DECREASE) ? mu * a.sigma : a.sigma * mu_c;
         }
         if (status < 0 && red[5] != 0.0) status = MO_QP_NONPOSITIVE_SLACK;  // F_ASSERT(all s > 0), qp.cc:285
-        if (status >= 0) break;
-        if (a.iter_log && lane == 0) {  // kkt_initial of the coming iteration (ComputeErrors with the new mu, qp.cc:118)
-          double* row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
-          const double cr = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
-          row[0] = sqrt(red[0]); row[1] = sqrt(cr > 0.0 ? cr : 0.0); row[2] = sqrt(red[1]); row[3] = sqrt(red[2]);
+        if (status < 0) {
+          if (a.iter_log && lane == 0) {  // kkt_initial of the coming iteration (ComputeErrors with the new mu, qp.cc:118)
+            double* row = a.iter_log + (prob * a.max_iterations + iters) * MO_QP_ITER_LOG_STRIDE;
+            const double cr = red[3] - 2 * (red[4] * mu) + (mu * mu) * M;
+            row[0] = sqrt(red[0]); row[1] = sqrt(cr > 0.0 ? cr : 0.0); row[2] = sqrt(red[1]); row[3] = sqrt(red[2]);
+          }
+          // (4) ComputeLDLT assembly (qp.cc:289-297): Sigma on the diagonal; rhs = -[r_aug; r_pe]
+#pragma unroll
+          for (int i = 0; i < VPL; ++i) {
+            const int v = lane + 32 * i;
+            rhsv[i] = -fma(-mu, t2[i], t1[i]);
+            if (v < N) {
+              const int jv = v >> 3, rr = v & 7;
+              T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2) + (rr >> 2) * 32 + rr * 4 + (rr & 3)] += w0[i] + w1[i];
+            }
+          }
+          rhse = -pe;
         }
-        // (4) ComputeLDLT assembly (qp.cc:289-297): Sigma on the diagonal; rhs = -[r_aug; r_pe]
+        }  // main_warp
+      }
+      // right-hand side into row 0 of tile row NT
+      if (main_warp && status < 0) {
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
           const int v = lane + 32 * i;
-          rhsv[i] = -fma(-mu, t2[i], t1[i]);
           if (v < N) {
-            const int jv = v >> 3, rr = v & 7;
-            T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2) + (rr >> 2) * 32 + rr * 4 + (rr & 3)] += w0[i] + w1[i];
+            const int jv = v >> 3, cc = v & 7;
+            T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2 + (NT - jv)) + (cc >> 2) * 32 + (cc & 3)] = rhsv[i];
           }
         }
-        rhse = -pe;
-      }
-      // right-hand side into row 0 of tile row NT
-#pragma unroll
-      for (int i = 0; i < VPL; ++i) {
-        const int v = lane + 32 * i;
-        if (v < N) {
-          const int jv = v >> 3, cc = v & 7;
-          T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2 + (NT - jv)) + (cc >> 2) * 32 + (cc & 3)] = rhsv[i];
+        if (isy) {
+          const int e = N + lane, je = e >> 3, cc = e & 7;
+          T[64 * (je * L::NTR - (je * (je - 1)) / 2 + (NT - je)) + (cc >> 2) * 32 + (cc & 3)] = rhse;
         }
       }
-      if (isy) {
-        const int e = N + lane, je = e >> 3, cc = e & 7;
-        T[64 * (je * L::NTR - (je * (je - 1)) / 2 + (NT - je)) + (cc >> 2) * 32 + (cc & 3)] = rhse;
+      if (NW == 2) {  // the helper learns whether the loop goes on
+        if (threadIdx.x == 0) *ctl = status;
+        __syncthreads();
+        status = *ctl;
+      } else {
+        __syncwarp();
       }
-      __syncwarp();
-      const bool ok = wd_factor_solve<N, K>(sm, lane);
+      if (status >= 0) break;
+      bool ok = wd_factor_solve<N, K, NW>(sm, lane, warp, Gp, Ap);
+      if (NW == 2) {
+        if (threadIdx.x == 0) *ctl = ok ? 1 : 0;
+        __syncthreads();  // also: the back substitution is done, the tiles are free for the next trip's staging
+        ok = *ctl != 0;
+      }
       if (!ok) { status = MO_QP_FAILED_FACTORIZATION; break; }
-      wd_stage<N, K>(T, Gp, Ap, lane);  // next trip's G, A: overlaps the update below
+      if (!L::STAGE_IN_BACKSUB) wd_stage<N, K, NW>(T, Gp, Ap, lane, warp);  // next trip's G, A: overlaps the update below
       WD_T(6);
       if (guess_pending) {  // x <- dx, y <- dy of the equality constrained solve (qp.cc:452-459), then clamp / s / z
         guess_pending = false;
+        if (main_warp) {
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) x[i] = XV[lane + 32 * i];
-        if (isy) y = -XV[N + lane];
-        clamp_init();
+          for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) x[i] = XV[lane + 32 * i];
+          if (isy) y = -XV[N + lane];
+          clamp_init();
+        }
+        wd_bar<NW>();  // XV consumed before the next trip republishes it
         continue;
       }
+      if (main_warp) {
       // (5) ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199)
       double al0 = 1.0, al1 = 1.0, dx[VPL], d0[VPL], d1[VPL], e0[VPL], e1[VPL];
 #pragma unroll
@@ -521,30 +675,33 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
         z0[i] = fma(e0[i], alpha_d, z0[i]); z1[i] = fma(e1[i], alpha_d, z1[i]);
       }
       if (isy) y = fma(-XV[N + lane], alpha_d, y);
+      }
       WD_T(7);
     }
     // ---- results ----
     cp_async_wait_all();
+    if (main_warp) {
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      const int v = lane + 32 * i;
-      if (v < N) {
-        vp[v] = x[i];
-        *reinterpret_cast<double2*>(vp + N + 2 * v) = make_double2(s0[i], s1[i]);
-        *reinterpret_cast<double2*>(vp + N + M + K + 2 * v) = make_double2(z0[i], z1[i]);
+      for (int i = 0; i < VPL; ++i) {
+        const int v = lane + 32 * i;
+        if (v < N) {
+          vp[v] = x[i];
+          *reinterpret_cast<double2*>(vp + N + 2 * v) = make_double2(s0[i], s1[i]);
+          *reinterpret_cast<double2*>(vp + N + M + K + 2 * v) = make_double2(z0[i], z1[i]);
+        }
       }
-    }
-    if (isy) vp[N + M + lane] = y;
-    if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
-      const double mn = wd_min(isy ? y : 1.0e300), li = -wd_min(isy ? -fabs(y) : 0.0);
-      if (lane == 0) { a.lagrange[prob * 2] = mn; a.lagrange[prob * 2 + 1] = li; }
-    }
-    if (lane == 0) {
-      a.status[prob] = status;
-      a.iters[prob] = iters;
-      if (a.kkt_final) {
-        double* kf = a.kkt_final + prob * 4;
-        kf[0] = kkt[0]; kf[1] = kkt[1]; kf[2] = kkt[2]; kf[3] = kkt[3];
+      if (isy) vp[N + M + lane] = y;
+      if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
+        const double mn = wd_min(isy ? y : 1.0e300), li = -wd_min(isy ? -fabs(y) : 0.0);
+        if (lane == 0) { a.lagrange[prob * 2] = mn; a.lagrange[prob * 2 + 1] = li; }
+      }
+      if (lane == 0) {
+        a.status[prob] = status;
+        a.iters[prob] = iters;
+        if (a.kkt_final) {
+          double* kf = a.kkt_final + prob * 4;
+          kf[0] = kkt[0]; kf[1] = kkt[1]; kf[2] = kkt[2]; kf[3] = kkt[3];
+        }
       }
     }
     WD_T(8);
@@ -553,7 +710,6 @@ __global__ void __launch_bounds__(32, MINB) qp_wd_kernel(const QPArgs a) {
   if (blockIdx.x == 0 && threadIdx.x == 0)
     printf("wd trace n=%d: matvec %lld | pervar+bookkeeping+rhs %lld | gather %lld | diag+inv %lld | panel %lld | backsub %lld | stage %lld | update %lld | results+load %lld\n",
            N, s_wd_tr[0], s_wd_tr[1], s_wd_tr[2], s_wd_tr[3], s_wd_tr[4], s_wd_tr[5], s_wd_tr[6], s_wd_tr[7], s_wd_tr[8]);
-
 #endif
 }
 

@@ -1,17 +1,20 @@
 // Launcher of the warp-per-problem DMMA kernel (qp_wdm.cuh) in its own translation unit: the kernel is the one under
 // active tuning and this keeps its rebuild at seconds. Called from dispatch_solve in capi.cu.
+#include <cstdlib>
+
 #include "qp_wdm.cuh"
 #include "wd_launch.h"
 
 namespace mo {
 
-// (N, K, min CTAs per SM)
-#define MO_WD_SHAPES(X) X(64, 16, 6) X(32, 8, 16) X(16, 8, 16)
+// (N, K, warps per problem, min CTAs per SM); MO_QP_WD_WARPS=1|2 overrides the warp count for A/B runs
+#define MO_WD_SHAPES(X) X(64, 16, 1, 6) X(32, 8, 1, 16) X(16, 8, 1, 16)
+#define MO_WD_ALT_SHAPES(X) X(64, 16, 2, 6) X(32, 8, 2, 12) X(16, 8, 2, 12)
 
-template <int N, int K, int MINB>
+template <int N, int K, int NW, int MINB>
 static cudaError_t launch_wd(const QPArgs& a, int sms, cudaStream_t stream) {
   using L = WdLayout<N, K>;
-  auto kernel = qp_wd_kernel<N, K, MINB>;
+  auto kernel = qp_wd_kernel<N, K, NW, MINB>;
   static thread_local int configured_dev = -1;
   static thread_local int bps = 0;
   int cur = 0;
@@ -20,26 +23,29 @@ static cudaError_t launch_wd(const QPArgs& a, int sms, cudaStream_t stream) {
   if (configured_dev != cur) {
     e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32, L::SMEM_BYTES);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32 * NW, L::SMEM_BYTES);
     if (e != cudaSuccess) return e;
     if (bps < 1) return cudaErrorInvalidConfiguration;
     configured_dev = cur;
   }
   const long long cap = (long long)sms * bps;
-  kernel<<<(int)(a.batch < cap ? a.batch : cap), 32, L::SMEM_BYTES, stream>>>(a);
+  kernel<<<(int)(a.batch < cap ? a.batch : cap), 32 * NW, L::SMEM_BYTES, stream>>>(a);
   return cudaGetLastError();
 }
 
 bool wd_has_shape(int n, int k) {
-#define X(N_, K_, B_) if (n == N_ && k == K_) return true;
+#define X(N_, K_, W_, B_) if (n == N_ && k == K_) return true;
   MO_WD_SHAPES(X)
 #undef X
   return false;
 }
 
 cudaError_t wd_launch(const QPArgs& a, int sms, cudaStream_t stream) {
-#define X(N_, K_, B_) if (a.n == N_ && a.k == K_) return launch_wd<N_, K_, B_>(a, sms, stream);
+  const char* e = getenv("MO_QP_WD_WARPS");
+  const int want = e ? atoi(e) : 0;
+#define X(N_, K_, W_, B_) if (a.n == N_ && a.k == K_ && (want == 0 || want == W_)) return launch_wd<N_, K_, W_, B_>(a, sms, stream);
   MO_WD_SHAPES(X)
+  MO_WD_ALT_SHAPES(X)
 #undef X
   return cudaErrorInvalidValue;
 }
