@@ -310,7 +310,8 @@ const char* mo_last_error_string(void) { return g_last_error.c_str(); }
 
 const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags) {
   if (tpp_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY)) return "tpp";
-  if (dm_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY)) return "dmma";
+  if (dm_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY))
+    return (!dm_use_cta_kernel() && mo::wd_has_shape(n, k)) ? "dmma_warp" : "dmma_cta";
   switch (generic_threads(n, k)) {
     case 32: return "generic32";
     case 128: return "generic128";

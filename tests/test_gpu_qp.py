@@ -285,19 +285,34 @@ def test_full_size_properties(dev):
     assert torch.equal(out2.vars, out.vars[:50000][perm]) and torch.equal(out2.iters, out.iters[:50000][perm])
 
 
+# The three DMMA kernels behind the same shapes: warp per problem (default), its two-warp look-ahead variant, and the
+# CTA-per-problem kernel; selected per call through the environment (read at dispatch time).
+DMMA_VARIANTS = {"warp": {"MO_QP_WD_WARPS": "1"}, "warp2": {"MO_QP_WD_WARPS": "2"}, "cta": {"MO_QP_DM_KERNEL": "cta"}}
+
+
+@pytest.fixture
+def dmma_variant(request, monkeypatch):
+    monkeypatch.delenv("MO_QP_WD_WARPS", raising=False)
+    monkeypatch.delenv("MO_QP_DM_KERNEL", raising=False)
+    for key, val in DMMA_VARIANTS[request.param].items():
+        monkeypatch.setenv(key, val)
+    return request.param
+
+
 @pytest.mark.gpu
+@pytest.mark.parametrize("dmma_variant", list(DMMA_VARIANTS), indirect=True)
 @pytest.mark.parametrize("n,k,B", [(64, 16, 8192), (32, 8, 16384), (16, 8, 16384)])
-def test_dmma_shapes_properties_and_determinism(dev, n, k, B):
-    """CTA-per-problem DMMA kernel at a batch that fills every SM with its full residency (4+ CTAs per SM, rotated
-    warp roles): KKT residuals recomputed on the host side in torch, and bit-identical results across repeated runs
-    and under a batch permutation (a shared-memory race or state leaking between the problems of a persistent CTA
-    shows up as nondeterminism)."""
+def test_dmma_shapes_properties_and_determinism(dev, n, k, B, dmma_variant):
+    """DMMA kernels at a batch that fills every SM with its full residency: KKT residuals recomputed on the host side
+    in torch, and bit-identical results across repeated runs and under a batch permutation (a shared-memory race or
+    state leaking between the problems of a persistent CTA shows up as nondeterminism)."""
     import torch
     from mini_opt_b200 import qp, lib
     m = 2 * n
     arrs = synth.box_qp_batch_torch(n, k, B, seed=11, device=dev)
     prm = synth.solve_params()
-    assert lib.load().mo_qp_kernel_variant(n, k, m, arrs.flags).decode() == "dmma"
+    want = "dmma_cta" if dmma_variant == "cta" else "dmma_warp"
+    assert lib.load().mo_qp_kernel_variant(n, k, m, arrs.flags).decode() == want
     outs = []
     for _ in range(3):
         out = qp.alloc_out_torch(B, n, k, m, dev)
@@ -329,3 +344,34 @@ def test_dmma_shapes_properties_and_determinism(dev, n, k, B):
     qp.solve_batch_device(sub, prm, out2, dev)
     torch.cuda.synchronize()
     assert torch.equal(out2.vars, out.vars[:nb][perm]) and torch.equal(out2.iters, out.iters[:nb][perm])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,k,B", [(64, 16, 2048), (32, 8, 4096), (16, 8, 4096)])
+@pytest.mark.parametrize("guess", [abi.MO_GUESS_NAIVE, abi.MO_GUESS_SOLVE_EQUALITY_CONSTRAINED])
+def test_dmma_kernel_variants_agree(dev, monkeypatch, n, k, B, guess):
+    """The warp-per-problem kernel (1 and 2 warps) and the CTA-per-problem kernel factor the same KKT matrices in a
+    different order of operations (left-looking from shared-memory tiles vs right-looking in accumulator fragments):
+    same status and iteration count on >= 97 % of the problems (start points clamped onto a bound are
+    rounding-chaotic; NAIVE starts must agree on all), and x to relative 1e-9 where they do."""
+    import torch
+    from mini_opt_b200 import qp
+    m = 2 * n
+    arrs = synth.box_qp_batch_torch(n, k, B, seed=5, device=dev)
+    prm = synth.solve_params(guess=guess)
+    res = {}
+    for name, env in DMMA_VARIANTS.items():
+        monkeypatch.delenv("MO_QP_WD_WARPS", raising=False)
+        monkeypatch.delenv("MO_QP_DM_KERNEL", raising=False)
+        for key, val in env.items():
+            monkeypatch.setenv(key, val)
+        out = qp.alloc_out_torch(B, n, k, m, dev)
+        qp.solve_batch_device(arrs, prm, out, dev)
+        torch.cuda.synchronize()
+        res[name] = qp.out_to_numpy(out)
+    for name, ref_name in (("warp", "cta"), ("warp2", "cta"), ("warp2", "warp")):
+        got, ref = res[name], res[ref_name]
+        same = (got.iters == ref.iters) & (got.status == ref.status)
+        assert same.mean() >= (1.0 if guess == abi.MO_GUESS_NAIVE else 0.97), (name, same.mean())
+        rel = np.abs(got.vars[:, :n] - ref.vars[:, :n]).max(axis=1) / np.maximum(1.0, np.abs(ref.vars[:, :n]).max(axis=1))
+        assert rel[same].max() < 1e-9, (name, rel[same].max())
