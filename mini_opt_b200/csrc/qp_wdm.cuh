@@ -26,7 +26,11 @@ namespace mo {
 
 template <int N, int K>
 struct WdLayout {
-  static constexpr int P = N + K, NT = P / 8, NTN = N / 8, NTR = NT + 1, M = 2 * N;
+  // RHS_ROW: the right-hand side rides through the factorization as tile row NT (forward substitution for free).
+  // At n = 64 that row costs 5 KB and the 7th resident problem per SM; there the forward substitution is done
+  // block by block next to the diagonal block instead (wd_forward_block).
+  static constexpr bool RHS_ROW = N < 64;
+  static constexpr int P = N + K, NT = P / 8, NTN = N / 8, NTR = NT + (RHS_ROW ? 1 : 0), M = 2 * N;
   static constexpr int VPL = (N + 31) / 32;  // variables per lane
   // stage the next trip's G, A column by column inside the back substitution (measured: n = 64 19.85 -> 19.53 ms;
   // n = 32 / 16 slower, their loop is issue-bound) or in one piece after it
@@ -38,9 +42,11 @@ struct WdLayout {
   static constexpr int O_D = 64 * NTILES;   // pivots d[P]
   static constexpr int O_INVD = O_D + P;    // 1 / d
   static constexpr int O_XV = O_INVD + P;   // [x; -y] for the matvec, then the solution [dx; -dy]
-  static constexpr int O_R = O_XV + P;      // K [x; -y]
-  static constexpr int O_RC = O_R + P;      // two-warp variant: the helper warp's column sums of the matvec [N]
-  static constexpr int O_CTL = O_RC + N;    // two-warp variant: status broadcast
+  static constexpr int O_R = O_XV + P;      // K [x; -y]; !RHS_ROW: then the right-hand side
+  static constexpr int O_W = O_R + P;       // !RHS_ROW: w = D^-1 L^-1 rhs [P]
+  static constexpr int O_RC = O_W;          // two-warp variant: the helper warp's column sums of the matvec [N] (aliases
+                                            // w: written in the matvec phase, w lives from factorization to back substitution)
+  static constexpr int O_CTL = O_W + P;     // two-warp variant: status broadcast
   static constexpr int TOTAL = O_CTL + 2;
   static constexpr size_t SMEM_BYTES = sizeof(double) * TOTAL;
 };
@@ -181,6 +187,39 @@ __device__ __noinline__ void wd_diag_block(double* __restrict__ tile, double* __
   __syncwarp();
 }
 
+// Forward substitution of block J when the right-hand side is not a tile row (WdLayout::RHS_ROW == false):
+// w_J = D_J^-1 S_J (b_J - sum_{kk < J} L(J,kk) D_kk w_kk), b in sm[O_R], w in sm[O_W]. Row sums over q (2 shuffle
+// levels), then S_J read transposed so that t[r] is already where it is needed (3 levels).
+template <int N, int K, int J>
+__device__ __forceinline__ void wd_forward_block(double* __restrict__ sm, int lane) {
+  using L = WdLayout<N, K>;
+  const int r = lane >> 2, q = lane & 3;
+  const double* __restrict__ T = sm;
+  const double* __restrict__ D = sm + L::O_D;
+  double* __restrict__ W = sm + L::O_W;
+  double sa = 0.0, sb = 0.0, sc = 0.0, sd = 0.0;
+#pragma unroll
+  for (int kk = 0; kk < J; ++kk) {
+    const double* __restrict__ t = T + L::tile(J, kk);
+    const double z0 = W[8 * kk + q] * D[8 * kk + q], z1 = W[8 * kk + 4 + q] * D[8 * kk + 4 + q];
+    if (kk & 1) { sc = fma(t[lane], z0, sc); sd = fma(t[32 + lane], z1, sd); }
+    else { sa = fma(t[lane], z0, sa); sb = fma(t[32 + lane], z1, sb); }
+  }
+  double s = (sa + sb) + (sc + sd);
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  const double tr = sm[L::O_R + 8 * J + r] - s;  // t[r] (replicated over q)
+  const int toff = (r >> 2) * 32 + q * 4 + (r & 3);
+  const double* __restrict__ S = T + L::tile(J, J);
+  double z0 = S[toff] * tr, z1 = S[toff + 16] * tr;  // S[4h + q][r] t[r]
+  z0 = wd_sum_r(z0); z1 = wd_sum_r(z1);
+  if (r == 0) {
+    W[8 * J + q] = z0 * sm[L::O_INVD + 8 * J + q];
+    W[8 * J + 4 + q] = z1 * sm[L::O_INVD + 8 * J + 4 + q];
+  }
+  __syncwarp();
+}
+
 // Block column J of the left-looking factorization: gather the updates of all earlier panels into the accumulator
 // fragments of tiles (J..NT, J), factor the diagonal block, solve the panel (and the right-hand-side row) with DMMA
 // against T = inv(L_JJ)' D_J^-1.
@@ -220,6 +259,7 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
   __syncwarp();
   WD_T(2);
   wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, chk);
+  if constexpr (!L::RHS_ROW) wd_forward_block<N, K, J>(sm, lane);
   WD_T(3);
   const double idr = sm[L::O_INVD + 8 * J + r];
   const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
@@ -250,12 +290,14 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
   double* __restrict__ T = sm;
   const int r = lane >> 2, q = lane & 3;
   const int coff = (q >> 1) * 32 + r * 4 + 2 * (q & 1);
-  double acc[CP][2];
+  constexpr int CPA = CP > 0 ? CP : 1;
+  double acc[CPA][2];
   if (warp == 0) {
     wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, chk);
+    if constexpr (!L::RHS_ROW) wd_forward_block<N, K, J>(sm, lane);
     const double idr = sm[L::O_INVD + 8 * J + r];
     const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
-    double f0[CP], f1[CP];
+    double f0[CPA], f1[CPA];
 #pragma unroll
     for (int i = 0; i < CP; ++i) { f0[i] = T[L::tile(J + 1 + i, J) + lane]; f1[i] = T[L::tile(J + 1 + i, J) + 32 + lane]; }
     __syncwarp();
@@ -277,7 +319,7 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
       const double* __restrict__ tb = T + L::tile(J + 1, kk);
       const double b0 = tb[lane] * -sm[L::O_D + 8 * kk + q];
       const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * kk + 4 + q];
-      double a0[CP], a1[CP];
+      double a0[CPA], a1[CPA];
 #pragma unroll
       for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
 #pragma unroll
@@ -294,7 +336,7 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
       const double* __restrict__ tb = T + L::tile(J + 1, J);
       const double b0 = tb[lane] * -sm[L::O_D + 8 * J + q];
       const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * J + 4 + q];
-      double a0[CP], a1[CP];
+      double a0[CPA], a1[CPA];
 #pragma unroll
       for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
 #pragma unroll
@@ -356,8 +398,8 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
     double sq = (sa + sb) + (sc + sd);
     sq += __shfl_xor_sync(0xffffffffu, sq, 1);
     sq += __shfl_xor_sync(0xffffffffu, sq, 2);
-    const double* __restrict__ w = tj + 64 * (L::NT - J);
-    const double tr = w[(r >> 2) * 32 + (r & 3)] - sq;   // t[r] (replicated over q)
+    const double wr = L::RHS_ROW ? tj[64 * (L::NT - J) + (r >> 2) * 32 + (r & 3)] : sm[L::O_W + 8 * J + r];
+    const double tr = wr - sq;                           // t[r] (replicated over q)
     double x0 = tj[lane] * tr, x1 = tj[32 + lane] * tr;  // S[r][4h + q] t[r]
     x0 = wd_sum_r(x0); x1 = wd_sum_r(x1);
     if (r == 0) { XS[8 * J + q] = x0; XS[8 * J + 4 + q] = x1; }
@@ -420,7 +462,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
     wd_bar<NW>();
     wd_stage<N, K, NW>(T, Gp, Ap, lane, warp);
     // right-hand-side tile row: rows 1..7 stay zero for the life of the problem
-    if (helper) {
+    if (helper && L::RHS_ROW) {
 #pragma unroll
       for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + lane] = 0.0; }
     }
@@ -606,8 +648,13 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         }
         }  // main_warp
       }
-      // right-hand side into row 0 of tile row NT
-      if (main_warp && status < 0) {
+      // right-hand side into row 0 of tile row NT, or into the vector the block forward substitution reads
+      if (main_warp && status < 0 && !L::RHS_ROW) {
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) if (lane + 32 * i < N) R[lane + 32 * i] = rhsv[i];
+        if (isy) R[N + lane] = rhse;
+      }
+      if (main_warp && status < 0 && L::RHS_ROW) {
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
           const int v = lane + 32 * i;

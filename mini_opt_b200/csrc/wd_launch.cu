@@ -10,7 +10,7 @@ namespace mo {
 // (N, K, warps per problem, min CTAs per SM); MO_QP_WD_WARPS=1|2 overrides the warp count for A/B runs.
 // Measured on B200 (ms per batch): n=64 64K QPs: 6 CTAs/SM (smem limit) 18.9; n=32 256K: 12 CTAs/SM (168 registers, no
 // spills) 18.5, 16 (128 registers) 19.6, 20 (96) 23.4; n=16 512K: 12 -> 19.3, 16 -> 19.1, 24 -> 23.5.
-#define MO_WD_SHAPES(X) X(64, 16, 1, 6) X(32, 8, 1, 12) X(16, 8, 1, 16)
+#define MO_WD_SHAPES(X) X(64, 16, 1, 7) X(32, 8, 1, 12) X(16, 8, 1, 16)
 #define MO_WD_ALT_SHAPES(X) X(64, 16, 2, 6) X(32, 8, 2, 12) X(16, 8, 2, 12)
 
 template <int N, int K, int NW, int MINB>
