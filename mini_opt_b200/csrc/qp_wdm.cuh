@@ -14,8 +14,8 @@
 // n = 32): 6 resp. 18+ independent problems per SM, no CTA barriers, and the pivot chains of different problems
 // overlap.
 //
-// Layout: tile (I, J), I >= J, 64 doubles, element [r][c] at (c >> 2) * 32 + r * 4 + (c & 3): lane l = 4 r + q of a
-// warp reads [r][4h + q] at h * 32 + l -- which is at once the DMMA A fragment of the tile and the B fragment of its
+// Layout: tile (I, J), I >= J, 64 doubles, element [r][c] at wd_el(r, c) = (c >> 2) * 32 + r' * 4 + (c & 3) with r' = r
+// (first half) or r ^ 2 (second half): lane l = 4 r + q of a warp reads [r][4h + q] at l resp. 32 + (l ^ 8) -- which is at once the DMMA A fragment of the tile and the B fragment of its
 // transpose, 256 contiguous bytes, bank-conflict free. Tile row NT (one past the matrix) carries the right-hand side
 // in its row 0, so the forward substitution and the D^-1 scaling fall out of the panel solve.
 #pragma once
@@ -60,6 +60,14 @@ __shared__ long long s_wd_t0;
 #define WD_T(i) do {} while (0)
 #endif
 
+// Offset of element [r][c] inside a tile: two 8x4 halves (columns 0-3, 4-7) of 32 doubles, row-major; the rows of the
+// second half are XOR-swizzled by 2 so that the 16-byte accumulator-fragment accesses of a quarter warp (rows 2a, 2a+1
+// of BOTH halves) fall into 32 distinct banks (unswizzled: 2-way conflicts on every accumulator load / store, 13 % of
+// all shared-memory wavefronts with the pipe 62 % busy, profiles/r01_wd64_ncu_full_summary.txt).
+__host__ __device__ __forceinline__ constexpr int wd_el(int r, int c) {
+  return (c >> 2) * 32 + (((c >> 2) ? (r ^ 2) : r) << 2) + (c & 3);
+}
+
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
   const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gsrc) : "memory");
@@ -99,14 +107,14 @@ __device__ __forceinline__ void wd_stage(double* __restrict__ T, const double* _
     for (int I = J; I < L::NTN; ++I, ++cnt) {
       if (NW == 1 || (cnt % NW) == warp) {
         cp_async8(T + L::tile(I, J) + lane, g + (8 * J) * N + 8 * I);
-        cp_async8(T + L::tile(I, J) + 32 + lane, g + (8 * J + 4) * N + 8 * I);
+        cp_async8(T + L::tile(I, J) + 32 + (lane ^ 8), g + (8 * J + 4) * N + 8 * I);
       }
     }
 #pragma unroll
     for (int I = L::NTN; I < L::NT; ++I, ++cnt) {
       if (NW == 1 || (cnt % NW) == warp) {
         cp_async8(T + L::tile(I, J) + lane, a + (8 * J) * K + 8 * (I - L::NTN));
-        cp_async8(T + L::tile(I, J) + 32 + lane, a + (8 * J + 4) * K + 8 * (I - L::NTN));
+        cp_async8(T + L::tile(I, J) + 32 + (lane ^ 8), a + (8 * J + 4) * K + 8 * (I - L::NTN));
       }
     }
   }
@@ -129,7 +137,7 @@ __device__ __noinline__ void wd_diag_block(double* __restrict__ tile, double* __
   for (int i = 0; i < 8; ++i) {
 #pragma unroll
     for (int j = 0; j <= i; j += 2) {
-      const double2 v = *reinterpret_cast<const double2*>(tile + (j >> 2) * 32 + i * 4 + (j & 3));
+      const double2 v = *reinterpret_cast<const double2*>(tile + wd_el(i, j));
       A[i][j] = v.x;
       if (j + 1 <= i) A[i][j + 1] = v.y;
     }
@@ -182,7 +190,7 @@ __device__ __noinline__ void wd_diag_block(double* __restrict__ tile, double* __
   if (lane < 8) {
     d[lr] = myd; invd[lr] = myinv;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) tile[(lr >> 2) * 32 + i * 4 + (lr & 3)] = x[i];  // S[i][lr]
+    for (int i = 0; i < 8; ++i) tile[wd_el(i, lr)] = x[i];  // S[i][lr]
   }
   __syncwarp();
 }
@@ -202,14 +210,14 @@ __device__ __forceinline__ void wd_forward_block(double* __restrict__ sm, int la
   for (int kk = 0; kk < J; ++kk) {
     const double* __restrict__ t = T + L::tile(J, kk);
     const double z0 = W[8 * kk + q] * D[8 * kk + q], z1 = W[8 * kk + 4 + q] * D[8 * kk + 4 + q];
-    if (kk & 1) { sc = fma(t[lane], z0, sc); sd = fma(t[32 + lane], z1, sd); }
-    else { sa = fma(t[lane], z0, sa); sb = fma(t[32 + lane], z1, sb); }
+    if (kk & 1) { sc = fma(t[lane], z0, sc); sd = fma(t[32 + (lane ^ 8)], z1, sd); }
+    else { sa = fma(t[lane], z0, sa); sb = fma(t[32 + (lane ^ 8)], z1, sb); }
   }
   double s = (sa + sb) + (sc + sd);
   s += __shfl_xor_sync(0xffffffffu, s, 1);
   s += __shfl_xor_sync(0xffffffffu, s, 2);
   const double tr = sm[L::O_R + 8 * J + r] - s;  // t[r] (replicated over q)
-  const int toff = (r >> 2) * 32 + q * 4 + (r & 3);
+  const int toff = wd_el(q, r);  // element [q][r]; [4 + q][r] is 16 further
   const double* __restrict__ S = T + L::tile(J, J);
   double z0 = S[toff] * tr, z1 = S[toff + 16] * tr;  // S[4h + q][r] t[r]
   z0 = wd_sum_r(z0); z1 = wd_sum_r(z1);
@@ -229,7 +237,7 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
   constexpr int CNT = L::NTR - J;
   double* __restrict__ T = sm;
   const int r = lane >> 2, q = lane & 3;
-  const int coff = (q >> 1) * 32 + r * 4 + 2 * (q & 1);  // accumulator fragment: [r][2q], [r][2q+1]
+  const int coff = wd_el(r, 2 * q);  // accumulator fragment: [r][2q], [r][2q+1]
   double acc[CNT][2];
 #pragma unroll
   for (int i = 0; i < CNT; ++i) {
@@ -243,10 +251,10 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
     for (int kk = 0; kk < J; ++kk) {
       const double* __restrict__ tb = T + L::tile(J, kk);
       const double b0 = tb[lane] * -sm[L::O_D + 8 * kk + q];
-      const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * kk + 4 + q];
+      const double b1 = tb[32 + (lane ^ 8)] * -sm[L::O_D + 8 * kk + 4 + q];
       double a0[CNT], a1[CNT];
 #pragma unroll
-      for (int i = 0; i < CNT; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
+      for (int i = 0; i < CNT; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + (lane ^ 8)]; }
 #pragma unroll
       for (int i = 0; i < CNT; ++i) dmma884(acc[i][0], acc[i][1], a0[i], b0);
 #pragma unroll
@@ -262,10 +270,10 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
   if constexpr (!L::RHS_ROW) wd_forward_block<N, K, J>(sm, lane);
   WD_T(3);
   const double idr = sm[L::O_INVD + 8 * J + r];
-  const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
+  const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + (lane ^ 8)] * idr;
   double a0[CNT], a1[CNT];
 #pragma unroll
-  for (int i = 1; i < CNT; ++i) { a0[i] = T[L::tile(J + i, J) + lane]; a1[i] = T[L::tile(J + i, J) + 32 + lane]; }
+  for (int i = 1; i < CNT; ++i) { a0[i] = T[L::tile(J + i, J) + lane]; a1[i] = T[L::tile(J + i, J) + 32 + (lane ^ 8)]; }
   __syncwarp();
 #pragma unroll
   for (int i = 1; i < CNT; ++i) {
@@ -289,17 +297,17 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
   constexpr bool HASN = J + 1 < L::NT;    // a block column J+1 exists
   double* __restrict__ T = sm;
   const int r = lane >> 2, q = lane & 3;
-  const int coff = (q >> 1) * 32 + r * 4 + 2 * (q & 1);
+  const int coff = wd_el(r, 2 * q);
   constexpr int CPA = CP > 0 ? CP : 1;
   double acc[CPA][2];
   if (warp == 0) {
     wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, chk);
     if constexpr (!L::RHS_ROW) wd_forward_block<N, K, J>(sm, lane);
     const double idr = sm[L::O_INVD + 8 * J + r];
-    const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + lane] * idr;
+    const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + (lane ^ 8)] * idr;
     double f0[CPA], f1[CPA];
 #pragma unroll
-    for (int i = 0; i < CP; ++i) { f0[i] = T[L::tile(J + 1 + i, J) + lane]; f1[i] = T[L::tile(J + 1 + i, J) + 32 + lane]; }
+    for (int i = 0; i < CP; ++i) { f0[i] = T[L::tile(J + 1 + i, J) + lane]; f1[i] = T[L::tile(J + 1 + i, J) + 32 + (lane ^ 8)]; }
     __syncwarp();
 #pragma unroll
     for (int i = 0; i < CP; ++i) {
@@ -318,10 +326,10 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
     for (int kk = 0; kk < J; ++kk) {
       const double* __restrict__ tb = T + L::tile(J + 1, kk);
       const double b0 = tb[lane] * -sm[L::O_D + 8 * kk + q];
-      const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * kk + 4 + q];
+      const double b1 = tb[32 + (lane ^ 8)] * -sm[L::O_D + 8 * kk + 4 + q];
       double a0[CPA], a1[CPA];
 #pragma unroll
-      for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
+      for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + (lane ^ 8)]; }
 #pragma unroll
       for (int i = 0; i < CP; ++i) dmma884(acc[i][0], acc[i][1], a0[i], b0);
 #pragma unroll
@@ -335,10 +343,10 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
     if (warp == 1) {
       const double* __restrict__ tb = T + L::tile(J + 1, J);
       const double b0 = tb[lane] * -sm[L::O_D + 8 * J + q];
-      const double b1 = tb[32 + lane] * -sm[L::O_D + 8 * J + 4 + q];
+      const double b1 = tb[32 + (lane ^ 8)] * -sm[L::O_D + 8 * J + 4 + q];
       double a0[CPA], a1[CPA];
 #pragma unroll
-      for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + lane]; }
+      for (int i = 0; i < CP; ++i) { a0[i] = tb[64 * i + lane]; a1[i] = tb[64 * i + 32 + (lane ^ 8)]; }
 #pragma unroll
       for (int i = 0; i < CP; ++i) {
         double e0 = 0.0, e1 = 0.0;  // second k-half in its own accumulator: two independent DMMAs per tile
@@ -384,7 +392,7 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
     // t[r] = w[r] - sum_I sum_k L(I,J)[k][r] x_I[k]: the tiles are read TRANSPOSED (element [4h + q][r], two contiguous
     // 128-byte runs per request in this layout), so the sum over k is two accumulators per lane plus a reduction over
     // q (2 shuffle levels), and t lands where the second product needs it (lane group r) without a broadcast.
-    const int toff = (r >> 2) * 32 + q * 4 + (r & 3);
+    const int toff = wd_el(q, r);  // element [q][r]; [4 + q][r] is 16 further
     double sa = 0.0, sb = 0.0, sc = 0.0, sd = 0.0;
     for (int I = J + 1; I < L::NT; I += 2) {
       const double* __restrict__ ti = tj + 64 * (I - J);
@@ -398,24 +406,25 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
     double sq = (sa + sb) + (sc + sd);
     sq += __shfl_xor_sync(0xffffffffu, sq, 1);
     sq += __shfl_xor_sync(0xffffffffu, sq, 2);
-    const double wr = L::RHS_ROW ? tj[64 * (L::NT - J) + (r >> 2) * 32 + (r & 3)] : sm[L::O_W + 8 * J + r];
+    const double wr = L::RHS_ROW ? tj[64 * (L::NT - J) + wd_el(0, r)] : sm[L::O_W + 8 * J + r];
     const double tr = wr - sq;                           // t[r] (replicated over q)
-    double x0 = tj[lane] * tr, x1 = tj[32 + lane] * tr;  // S[r][4h + q] t[r]
+    double x0 = tj[lane] * tr, x1 = tj[32 + (lane ^ 8)] * tr;  // S[r][4h + q] t[r]
     x0 = wd_sum_r(x0); x1 = wd_sum_r(x1);
     if (r == 0) { XS[8 * J + q] = x0; XS[8 * J + 4 + q] = x1; }
     __syncwarp();
     // block column J of L is consumed: stage the next trip's G, A into it now, under the rest of the substitution
     if (kStageInBacksub && J < L::NTN) {
       double* __restrict__ dst = sm + 64 * (J * L::NTR - (J * (J - 1)) / 2) + lane;
+      const int hi = 32 + (lane ^ 8) - lane;  // second half of the tile, swizzled
       const double* __restrict__ g = Gp + (q + 8 * J) * N + r + 8 * J;
       for (int I = J; I < L::NTN; ++I, dst += 64, g += 8) {
         cp_async8(dst, g);
-        cp_async8(dst + 32, g + 4 * N);
+        cp_async8(dst + hi, g + 4 * N);
       }
       const double* __restrict__ ap = Ap + (q + 8 * J) * K + r;
       for (int I = L::NTN; I < L::NT; ++I, dst += 64, ap += 8) {
         cp_async8(dst, ap);
-        cp_async8(dst + 32, ap + 4 * K);
+        cp_async8(dst + hi, ap + 4 * K);
       }
     }
   }
@@ -464,7 +473,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
     // right-hand-side tile row: rows 1..7 stay zero for the life of the problem
     if (helper && L::RHS_ROW) {
 #pragma unroll
-      for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + lane] = 0.0; }
+      for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + (lane ^ 8)] = 0.0; }
     }
     double x[VPL], s0[VPL], s1[VPL], z0[VPL], z1[VPL], b0[VPL], b1[VPL], cv[VPL];
 #pragma unroll
@@ -529,7 +538,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
 #pragma unroll
         for (int J = NTN; J < NT; ++J)
 #pragma unroll
-          for (int I = J; I < NT; ++I) { T[L::tile(I, J) + lane] = 0.0; T[L::tile(I, J) + 32 + lane] = 0.0; }
+          for (int I = J; I < NT; ++I) { T[L::tile(I, J) + lane] = 0.0; T[L::tile(I, J) + 32 + (lane ^ 8)] = 0.0; }
       }
       if (guess_pending) {  // KKT system without Sigma, rhs = -[c; b_eq]
 #pragma unroll
@@ -548,7 +557,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
           const double vr = XV[8 * I + r];
 #pragma unroll
           for (int J = 0; J <= (I < NTN ? I : NTN - 1); ++J) {
-            const double e0 = T[L::tile(I, J) + lane], e1 = T[L::tile(I, J) + 32 + lane];  // [r][q], [r][4 + q]
+            const double e0 = T[L::tile(I, J) + lane], e1 = T[L::tile(I, J) + 32 + (lane ^ 8)];  // [r][q], [r][4 + q]
             const double v0 = XV[8 * J + q], v1 = XV[8 * J + 4 + q];
             if (I == J) {  // diagonal tile: lower triangle significant
               ra = q <= r ? fma(e0, v0, ra) : ra;
@@ -641,7 +650,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
             rhsv[i] = -fma(-mu, t2[i], t1[i]);
             if (v < N) {
               const int jv = v >> 3, rr = v & 7;
-              T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2) + (rr >> 2) * 32 + rr * 4 + (rr & 3)] += w0[i] + w1[i];
+              T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2) + wd_el(rr, rr)] += w0[i] + w1[i];
             }
           }
           rhse = -pe;
@@ -660,12 +669,12 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
           const int v = lane + 32 * i;
           if (v < N) {
             const int jv = v >> 3, cc = v & 7;
-            T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2 + (NT - jv)) + (cc >> 2) * 32 + (cc & 3)] = rhsv[i];
+            T[64 * (jv * L::NTR - (jv * (jv - 1)) / 2 + (NT - jv)) + wd_el(0, cc)] = rhsv[i];
           }
         }
         if (isy) {
           const int e = N + lane, je = e >> 3, cc = e & 7;
-          T[64 * (je * L::NTR - (je * (je - 1)) / 2 + (NT - je)) + (cc >> 2) * 32 + (cc & 3)] = rhse;
+          T[64 * (je * L::NTR - (je * (je - 1)) / 2 + (NT - je)) + wd_el(0, cc)] = rhse;
         }
       }
       if (NW == 2) {  // the helper learns whether the loop goes on
