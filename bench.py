@@ -218,8 +218,58 @@ def ik_main(args, rank, world, local):
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         dist.all_reduce(sm_, op=dist.ReduceOp.SUM)
         ms, qp_steps, ok = float(mx[0]), float(sm_[1]), float(sm_[2])
+    nls_iters = float(out.iterations.sum().item())
+    # algorithmic flops: F(n, k, m) per inner Newton step + per outer iteration the chain FK / Jacobians
+    # (~300 per link) and the linearization R N (N + 1) + 2 R N + N with R = cost rows
+    n_, m_, R_ = ch.n, ch.m, ch.n_cost
+    flops_local = qp_steps * flops_per_step(n_, ch.n_eq, m_) + nls_iters * (300.0 * args.links + R_ * n_ * (n_ + 1) + 2 * R_ * n_ + n_)
+    fl = torch.tensor([flops_local], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(fl, op=dist.ReduceOp.SUM)
+    fp64_peak = lib.measure_fp64_peak(local)
+    e2e = None
+    if not args.no_e2e:
+        pipe = nls.ChainIKHostPipeline(synth.chain_ik_batch_numpy(args.links, B, seed=4321 + rank), dev)
+        for _ in range(2):
+            pipe.solve(prm)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        n_e2e = max(2, min(args.steps, 3))
+        ts = time.perf_counter()
+        for _ in range(n_e2e):
+            hres = pipe.solve(prm)
+        sec = (time.perf_counter() - ts) / n_e2e
+        assert int(hres["qp_iterations"].sum()) == int(out.qp_iterations.sum().item()), "host pipeline disagrees with device path"
+        tsec = torch.tensor([sec], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tsec, op=dist.ReduceOp.MAX)
+        e2e = {"value": qp_steps / float(tsec[0]), "unit": UNIT, "h2d_bytes_per_step": int(pipe.h2d_bytes) * world,
+               "d2h_bytes_per_step": int(pipe.d2h_bytes) * world, "ms_per_step": 1e3 * float(tsec[0]),
+               "nls_problems_per_sec": B * world / float(tsec[0])}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import oracle_py as O  # bench cpu_baseline leg: the unmodified reference, timed as the checker's twin
+        sample = min(B, 20000)
+        chs = synth.chain_ik_batch_numpy(args.links, sample, seed=4321)
+        threads = host_cores()
+        O.nls_solve_chain("ref", synth.chain_ik_batch_numpy(args.links, 512, seed=1), prm, nthreads=threads)
+        tc = time.perf_counter()
+        _, total = O.nls_solve_chain("ref", chs, prm, nthreads=threads)
+        dtc = time.perf_counter() - tc
+        cpu = {"value": total / dtc, "unit": UNIT, "cores": threads, "kind": "reference",
+               "sample": f"{sample} problems of the same recipe, one ConstrainedNonlinearLeastSquares per std::thread",
+               "nls_problems_per_sec": sample / dtc, "seconds": dtc}
     if rank == 0:
-        print(json.dumps({"metric": METRIC, "value": qp_steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        tfl = float(fl[0]) / (ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "pipe": "fp64 (DFMA; the n <= 12 systems have no 8x8x4 contraction for DMMA)",
+                    "achieved": tfl, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tfl / fp64_peak, "traffic": None,
+                    "kernel": "nls_chain_ik_kernel", "kernel_ms": ms,
+                    "algorithmic_flops_per_launch": float(fl[0]),
+                    "peak_source": "DFMA microbenchmark measured live on this GPU (mo_measure_fp64_peak)",
+                    "note": "one warp per problem, dependent scalar chains: latency-bound, see DESIGN.md 3.2"}
+        print(json.dumps({"roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                          "metric": METRIC, "value": qp_steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                           "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
                           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                           "config": {"workload": f"config3: {B} transform-chain IK problems per GPU, {args.links} Z-revolute links, "

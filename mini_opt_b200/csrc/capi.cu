@@ -667,7 +667,13 @@ int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_
                         params->lambda_decrease_on_success, params->lambda_decrease_on_restore, params->max_lambda,
                         params->min_lambda, params->retraction, params->inner_qp_solver};
   const mo::NlsOut o{out->x, out->termination, out->iterations, out->qp_iterations, out->ls_steps, out->errors};
-  mo::nls_chain_ik_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(problems), p, o);
+  // ticket counter of this launch: a slot of a small ring in device memory, zeroed on the launch stream
+  static std::atomic<unsigned> ring{0};
+  unsigned long long* tickets = nullptr;
+  MO_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&tickets), mo::g_ik_tickets));
+  tickets += ring.fetch_add(1) % mo::kIkTicketSlots;
+  MO_CUDA(cudaMemsetAsync(tickets, 0, sizeof(unsigned long long), static_cast<cudaStream_t>(cuda_stream)));
+  mo::nls_chain_ik_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(problems), p, o, tickets);
   g_launches.fetch_add(1);
   MO_CUDA(cudaGetLastError());
   return MO_OK;

@@ -421,7 +421,21 @@ __host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost,
 #ifndef MO_IK_MINB
 #define MO_IK_MINB 24  // measured on B200 (6 links, 100K problems): 8 -> 769 ms, 16 -> 672, 24 -> 641, 32 -> 682
 #endif
-__global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out) {
+constexpr int kIkTicketSlots = 64;  // launches in flight that may hold a ticket counter at the same time
+__device__ unsigned long long g_ik_tickets[kIkTicketSlots];
+
+// Next problem of a persistent warp: the first gridDim.x problems are taken by block index, the rest from a global
+// ticket counter (zeroed on the launch stream). SQP iteration counts are heavy-tailed (a few % of the IK problems run
+// to max_iterations), so a static stride leaves most warps idle while the unlucky ones finish.
+__device__ __forceinline__ long long next_ticket(unsigned long long* __restrict__ ctr) {
+  unsigned long long t = 0;
+  if ((threadIdx.x & 31) == 0) t = atomicAdd(ctr, 1ULL);
+  t = __shfl_sync(0xffffffffu, t, 0);
+  return (long long)gridDim.x + (long long)t;
+}
+
+__global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out,
+                                                                      unsigned long long* __restrict__ ticket) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x, n = a.n, k = a.n_eq, m = a.m;
   ChainWork C;
@@ -448,7 +462,7 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
   const GenSolveParams sp{1.0, 0.1, prm.kkt_tol, 1.0e-6, prm.max_qp_iterations, MO_BARRIER_COMPLEMENTARITY, 0,
                           k ? MO_GUESS_SOLVE_EQUALITY_CONSTRAINED : MO_GUESS_NAIVE, 0};  // nonlinear.cc:226-239
   constexpr int kMaxSteps = 40;
-  for (long long p = blockIdx.x; p < a.batch; p += gridDim.x) {
+  for (long long p = blockIdx.x; p < a.batch; p = next_ticket(ticket)) {
     if (lane == 0) *C.have_cache = 0;
     for (int i = lane; i < n; i += 32) x[i] = a.x0[p * n + i];
     __syncwarp();

@@ -46,6 +46,42 @@ def solve_chain_ik_device(ch: abi.ChainIKArrays, params: abi.NLSParams, out: abi
                                                      st.cuda_stream))
 
 
+_CHAIN_ARRAYS = ("link_pose", "link_mask", "cost_w", "cost_target", "eq_w", "eq_target", "ineq_var", "ineq_a", "ineq_b", "x0")
+
+
+class ChainIKHostPipeline:
+    """Host-buffer path of the chain-IK solve for the harness (bench ``e2e``): the problem arrays live in pinned host
+    memory, every call copies them to preallocated device buffers, runs ``mo_nls_solve_chain_ik_batch`` and copies the
+    results back to pinned host memory, all on one stream. ``h2d_bytes`` / ``d2h_bytes`` are counted from the tensors."""
+
+    def __init__(self, ch: abi.ChainIKArrays, device):
+        import torch
+        self.device = device
+        kw = {f.name: getattr(ch, f.name) for f in dataclasses.fields(ch)}
+        self.host, self.dev = {}, {}
+        for name in _CHAIN_ARRAYS:
+            if kw[name] is not None:
+                self.host[name] = torch.from_numpy(np.ascontiguousarray(kw[name])).pin_memory()
+                self.dev[name] = torch.empty_like(self.host[name], device=device)
+        self.ch = abi.ChainIKArrays(**{**kw, **{k: self.dev.get(k) for k in _CHAIN_ARRAYS}})
+        self.out = alloc_nls_out_torch(ch.batch, ch.n, device)
+        self.host_out = {f.name: torch.empty_like(getattr(self.out, f.name), device="cpu").pin_memory()
+                         for f in dataclasses.fields(self.out)}
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
+        self.d2h_bytes = sum(t.numel() * t.element_size() for t in self.host_out.values())
+
+    def solve(self, params: abi.NLSParams):
+        import torch
+        st = torch.cuda.current_stream(self.device)
+        for name, h in self.host.items():
+            self.dev[name].copy_(h, non_blocking=True)
+        solve_chain_ik_device(self.ch, params, self.out, self.device, st)
+        for name, h in self.host_out.items():
+            h.copy_(getattr(self.out, name), non_blocking=True)
+        st.synchronize()
+        return self.host_out
+
+
 def chain_fk_device(ch: abi.ChainIKArrays, params_t, device):
     """``mo_chain_fk_batch``: dict(translation, rotation_q, t_D_params, r_D_params) of device tensors."""
     import torch
