@@ -1,0 +1,440 @@
+// C++ host API of mini_opt_b200 for the nonlinear least squares driver: the reference's class surface
+// (gareth-cross/mini_opt include/mini_opt/residual.hpp:25-143, include/mini_opt/nonlinear.hpp:24-157,
+// include/mini_opt/structs.hpp:150-248) with the Residual callbacks kept on the HOST and the QP solves batched on the
+// device. Header only; link with -lminiopt_b200.
+//
+// `ConstrainedNonlinearLeastSquares::SolveBatch` advances B independent problems of identical shape in lockstep: per
+// outer iteration every still-active problem is linearized on the host by its own Residual functors
+// (LinearizeAndFillQP, source/nonlinear.cc:170-214), all the QPs go to the device in ONE
+// QPInteriorPointSolver::SolveBatch call (ComputeStepDirection, :216-259), and the scalar SQP logic of Solve
+// (:75-158: ComputeQPCostDerivative :457-482, SelectPenalty :484-502, SelectStepSize :351-416 with both line search
+// strategies :418-605, UpdateLambdaAndCheckExitConditions :296-343) runs per problem on the host, where the user's
+// functors live. Problems whose residuals are transform chains can run entirely on the device instead
+// (mo_nls_solve_chain_ik_batch). Equality-only problems (the reference switches to QPNullSpaceSolver, :83-89) are
+// solved by the interior point kernel with M = 0, which Iterate supports (mu = 0).
+#pragma once
+
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <functional>
+#include <limits>
+#include <memory>
+#include <optional>
+#include <utility>
+
+#include "mini_opt_b200/qp.hpp"
+
+namespace mini_opt_b200 {
+
+enum class LineSearchStrategy { ARMIJO_BACKTRACK = 0, POLYNOMIAL_APPROXIMATION = 1 };  // structs.hpp:147-152
+enum class OptimizerState { NOMINAL = 0, ATTEMPTING_RESTORE_LM = 1 };                  // structs.hpp:155-158
+enum class StepSizeSelectionResult {                                                   // structs.hpp:208-221
+  SUCCESS = 0, MAX_ITERATIONS, FIRST_ORDER_SATISFIED, POSITIVE_DERIVATIVE, FAILURE_NON_FINITE_COST, FAILURE_INVALID_ALPHA
+};
+enum class NLSTerminationState {                                                       // structs.hpp:225-240
+  MAX_ITERATIONS, SATISFIED_ABSOLUTE_TOL, SATISFIED_RELATIVE_TOL, SATISFIED_FIRST_ORDER_TOL, MAX_LAMBDA, QP_INDEFINITE,
+  USER_CALLBACK
+};
+
+struct Errors {  // structs.hpp:169-186
+  double f{0}, equality{0};
+  double Total(double penalty) const { return f + penalty * equality; }
+  double LInfinity() const { return std::max(f, equality); }
+  bool ContainsInvalidValues() const { return !std::isfinite(f) || !std::isfinite(equality); }
+};
+struct DirectionalDerivatives {  // structs.hpp:189-199
+  double d_f{0}, d_equality{0};
+  double Total(double penalty) const { return d_f + penalty * d_equality; }
+  double LInfinity() const { return std::max(std::abs(d_f), std::abs(d_equality)); }
+};
+struct LineSearchStep { double alpha; Errors errors; };  // structs.hpp:202-205
+
+// One iteration of the outer loop (NLSIteration, structs.hpp:251-290, without the per-QP-iteration log).
+struct NLSIteration {
+  int iteration;
+  OptimizerState optimizer_state;
+  double lambda;
+  Errors errors_initial;
+  QPInteriorPointTerminationState qp_termination_state;
+  int qp_iterations;
+  DirectionalDerivatives directional_derivatives;
+  double penalty;
+  StepSizeSelectionResult step_result;
+  std::vector<LineSearchStep> line_search_steps;
+};
+struct NLSSolverOutputs {  // structs.hpp:293-301
+  NLSTerminationState termination_state = NLSTerminationState::MAX_ITERATIONS;
+  std::vector<NLSIteration> iterations;
+  Vector variables;  // batched API: the final variables travel with the outputs
+};
+
+// Type-erased residual (residual.hpp:25-118). `Model<R, P>` wraps a functor
+//   std::array<double, R> f(const std::array<double, P>& params, std::array<double, R * P>* J_or_null)
+// with J column-major R x P like Eigen::Matrix<double, R, P>.
+class Residual {
+ public:
+  struct Concept {
+    virtual ~Concept() = default;
+    virtual int Dimension() const = 0;
+    virtual const std::vector<int>& Index() const = 0;
+    // r[Dimension()], J (Dimension() x Index().size(), column-major) or nullptr
+    virtual void Evaluate(const Vector& params, double* r, double* J) const = 0;
+  };
+  template <int R, int P, class F>
+  struct Model final : Concept {
+    Model(const std::array<int, P>& index, F f) : index_(index.begin(), index.end()), func_(std::move(f)) {}
+    int Dimension() const override { return R; }
+    const std::vector<int>& Index() const override { return index_; }
+    void Evaluate(const Vector& params, double* r, double* J) const override {
+      std::array<double, P> p;  // GatherParams, residual.hpp:151-169
+      for (int i = 0; i < P; ++i) {
+        if (index_[i] < 0 || index_[i] >= params.rows()) throw std::out_of_range("Index exceeds the number of params");
+        p[i] = params[index_[i]];
+      }
+      std::array<double, R * P> Jl{};
+      const std::array<double, R> rv = func_(p, J ? &Jl : nullptr);
+      std::copy(rv.begin(), rv.end(), r);
+      if (J) std::copy(Jl.begin(), Jl.end(), J);
+    }
+    std::vector<int> index_;
+    F func_;
+  };
+
+  Residual() = default;
+  explicit Residual(std::shared_ptr<const Concept> impl) : impl_(std::move(impl)) {}
+  int Dimension() const { return impl_->Dimension(); }
+  const std::vector<int>& GetIndex() const { return impl_->Index(); }
+
+  // residual.hpp:175-180
+  void ErrorVector(const Vector& params, double* b_out) const { impl_->Evaluate(params, b_out, nullptr); }
+  double QuadraticError(const Vector& params) const {
+    std::vector<double> r(Dimension());
+    ErrorVector(params, r.data());
+    double s = 0;
+    for (double v : r) s += v * v;
+    return 0.5 * s;
+  }
+  // residual.hpp:186-226: H(lower) += J'J, b += J'r over the residual's parameter index; returns 1/2 |r|^2
+  double UpdateHessian(const Vector& params, Matrix* H, Vector* b) const {
+    const int R = Dimension(), N = static_cast<int>(GetIndex().size());
+    std::vector<double> r(R), J(static_cast<std::size_t>(R) * N);
+    impl_->Evaluate(params, r.data(), J.data());
+    for (int row_local = 0; row_local < N; ++row_local) {
+      const int row_global = GetIndex()[row_local];
+      for (int col_local = 0; col_local <= row_local; ++col_local) {
+        const int col_global = GetIndex()[col_local];
+        double JtT = 0;
+        for (int e = 0; e < R; ++e) JtT += J[row_local * R + e] * J[col_local * R + e];
+        if (col_global <= row_global) (*H)(row_global, col_global) += JtT;
+        else (*H)(col_global, row_global) += JtT;
+      }
+      double Jtr = 0;
+      for (int e = 0; e < R; ++e) Jtr += J[row_local * R + e] * r[e];
+      (*b)[row_global] += Jtr;
+    }
+    double s = 0;
+    for (double v : r) s += v * v;
+    return 0.5 * s;
+  }
+  // residual.hpp:230-250: rows [row, row + Dimension()) of A <- J scattered by index, of b <- r
+  void UpdateJacobian(const Vector& params, Matrix* A, Vector* b, int row) const {
+    const int R = Dimension(), N = static_cast<int>(GetIndex().size());
+    std::vector<double> r(R), J(static_cast<std::size_t>(R) * N);
+    impl_->Evaluate(params, r.data(), J.data());
+    for (int e = 0; e < R; ++e) (*b)[row + e] = r[e];
+    for (int col_local = 0; col_local < N; ++col_local)
+      for (int e = 0; e < R; ++e) (*A)(row + e, GetIndex()[col_local]) = J[col_local * R + e];
+  }
+
+ private:
+  std::shared_ptr<const Concept> impl_;
+};
+
+// residual.hpp:121-143
+template <int R, int P, class F>
+Residual MakeResidual(const std::array<int, P>& index, F&& f) {
+  return Residual(std::make_shared<Residual::Model<R, P, std::decay_t<F>>>(index, std::forward<F>(f)));
+}
+
+// nonlinear.hpp:24-35: min sum 1/2 |f_i(x)|^2  s.t.  c_j(x) = 0,  a x[v] + b >= 0
+struct Problem {
+  int dimension{0};
+  std::vector<Residual> costs;
+  std::vector<LinearInequalityConstraint> inequality_constraints;
+  std::vector<Residual> equality_constraints;
+  void clear() { costs.clear(); inequality_constraints.clear(); equality_constraints.clear(); }
+};
+
+class ConstrainedNonlinearLeastSquares {
+ public:
+  struct Params {  // nonlinear.hpp:37-124, same defaults
+    int max_iterations{10};
+    int max_qp_iterations{10};
+    double termination_kkt_tolerance{1.0e-6};
+    double absolute_exit_tol{1.0e-12};
+    double relative_exit_tol{1.0e-5};
+    double absolute_first_derivative_tol{1.0e-6};
+    int max_line_search_iterations{2};
+    LineSearchStrategy line_search_strategy{LineSearchStrategy::POLYNOMIAL_APPROXIMATION};
+    double armijo_search_tau{0.8};
+    double equality_penalty_initial{1.0};
+    double equality_penalty_scale_factor{1.01};
+    double equality_penalty_rho{0.1};
+    double lambda_initial{0.0};
+    double lambda_failure_init{1.0e-2};
+    double lambda_decrease_on_success{0.1};
+    double lambda_decrease_on_restore{0.8};
+    double max_lambda{1.};
+    double min_lambda{0.};
+  };
+  // nonlinear.hpp:127: x <- x (+) alpha * dx
+  using Retraction = std::function<void(Vector& x, const Vector& dx, double alpha)>;
+
+  explicit ConstrainedNonlinearLeastSquares(const Problem* problem, Retraction retraction = nullptr)
+      : p_(problem), custom_retraction_(std::move(retraction)) {
+    if (!p_) throw std::invalid_argument("Must have a valid problem");
+  }
+
+  // One problem = a batch of one.
+  NLSSolverOutputs Solve(const Params& params, const Vector& variables, int device = 0) {
+    std::vector<NLSSolverOutputs> out = SolveBatch({p_}, params, {variables}, custom_retraction_, device);
+    variables_ = out[0].variables;
+    return std::move(out[0]);
+  }
+  const Vector& variables() const { return variables_; }
+
+  // nonlinear.cc:279-293
+  static Errors EvaluateNonlinearErrors(const Problem& problem, const Vector& vars) {
+    Errors e{};
+    std::vector<double> buf;
+    for (const Residual& cost : problem.costs) {
+      buf.assign(cost.Dimension(), 0.0);
+      cost.ErrorVector(vars, buf.data());
+      double s = 0;
+      for (double v : buf) s += v * v;
+      e.f += 0.5 * s;
+    }
+    for (const Residual& eq : problem.equality_constraints) {
+      buf.assign(eq.Dimension(), 0.0);
+      eq.ErrorVector(vars, buf.data());
+      for (double v : buf) e.equality += std::abs(v);
+    }
+    return e;
+  }
+  Errors EvaluateNonlinearErrors(const Vector& vars) const { return EvaluateNonlinearErrors(*p_, vars); }
+
+  // nonlinear.cc:170-214
+  static Errors LinearizeAndFillQP(const Vector& variables, double lambda, const Problem& problem, QP* qp) {
+    const int n = problem.dimension;
+    int rows = 0;
+    for (const Residual& eq : problem.equality_constraints) rows += eq.Dimension();
+    qp->G.resize(n, n);
+    qp->c.assign(static_cast<std::size_t>(n), 0.0);
+    qp->A_eq.resize(rows, n);
+    qp->b_eq.assign(static_cast<std::size_t>(rows), 0.0);
+    Errors e{};
+    for (const Residual& cost : problem.costs) e.f += cost.UpdateHessian(variables, &qp->G, &qp->c);
+    if (lambda > 0)
+      for (int i = 0; i < n; ++i) qp->G(i, i) += lambda;
+    int row = 0;
+    for (const Residual& eq : problem.equality_constraints) {
+      eq.UpdateJacobian(variables, &qp->A_eq, &qp->b_eq, row);
+      for (int i = 0; i < eq.Dimension(); ++i) e.equality += std::abs(qp->b_eq[row + i]);
+      row += eq.Dimension();
+    }
+    qp->constraints.clear();
+    for (const LinearInequalityConstraint& c : problem.inequality_constraints) qp->constraints.push_back(c.ShiftTo(variables));
+    return e;
+  }
+
+  // Batched entry point: problems of identical shape (dimension, equality rows, inequality count), one start point
+  // each. The QPs of all active problems are solved in one device call per outer iteration.
+  static std::vector<NLSSolverOutputs> SolveBatch(const std::vector<const Problem*>& problems, const Params& params,
+                                                  const std::vector<Vector>& initial_variables,
+                                                  const Retraction& retraction = nullptr, int device = 0) {
+    CheckParams(params);
+    const std::size_t B = problems.size();
+    if (initial_variables.size() != B) throw std::invalid_argument("one start point per problem");
+    struct State {
+      Vector x, cand, dx;
+      double lambda, penalty;
+      OptimizerState state = OptimizerState::NOMINAL;
+      bool done = false;
+      QP qp;
+      Errors errors_pre;
+    };
+    std::vector<State> st(B);
+    std::vector<NLSSolverOutputs> out(B);
+    for (std::size_t i = 0; i < B; ++i) {
+      if (!problems[i]) throw std::invalid_argument("Must have a valid problem");
+      if (initial_variables[i].rows() != problems[i]->dimension) throw std::invalid_argument("variables / dimension mismatch");
+      st[i].x = initial_variables[i];
+      st[i].lambda = params.lambda_initial;
+      st[i].penalty = params.equality_penalty_initial;
+    }
+    QPInteriorPointSolver::Params qp_params;  // nonlinear.cc:226-239
+    qp_params.max_iterations = params.max_qp_iterations;
+    qp_params.termination_kkt_tol = params.termination_kkt_tolerance;
+    qp_params.initial_mu = 1.0;
+    qp_params.sigma = 0.1;
+    qp_params.initialize_mu_with_complementarity = false;
+    for (int iter = 0; iter < params.max_iterations; ++iter) {
+      std::vector<std::size_t> active;
+      std::vector<QP> qps;
+      for (std::size_t i = 0; i < B; ++i) {
+        if (st[i].done) continue;
+        st[i].errors_pre = LinearizeAndFillQP(st[i].x, st[i].lambda, *problems[i], &st[i].qp);
+        active.push_back(i);
+        qps.push_back(st[i].qp);
+      }
+      if (active.empty()) break;
+      qp_params.initial_guess_method = problems[active[0]]->equality_constraints.empty()
+                                           ? InitialGuessMethod::NAIVE : InitialGuessMethod::SOLVE_EQUALITY_CONSTRAINED;
+      const std::vector<QPInteriorPointSolverOutputs> sol = QPInteriorPointSolver::SolveBatch(qps, qp_params, device);
+      for (std::size_t a = 0; a < active.size(); ++a) {
+        const std::size_t i = active[a];
+        State& s = st[i];
+        const Problem& prob = *problems[i];
+        const QPInteriorPointSolverOutputs& q = sol[a];
+        if (q.batch_status == MO_QP_FAILED_FACTORIZATION) throw FailedFactorization("Failed to solve self-adjoint system");
+        const int n = prob.dimension;
+        s.dx.assign(q.variables.begin(), q.variables.begin() + n);
+        // ComputeQPCostDerivative, nonlinear.cc:457-482
+        DirectionalDerivatives dd{};
+        for (int j = 0; j < n; ++j) dd.d_f += s.qp.c[j] * s.dx[j];
+        for (int r = 0; r < s.qp.A_eq.rows(); ++r) {
+          const double b = s.qp.b_eq[r], sign = b > 0 ? 1.0 : (b < 0 ? -1.0 : 0.0);
+          double dot = 0;
+          for (int j = 0; j < n; ++j) dot += s.qp.A_eq(r, j) * s.dx[j];
+          dd.d_equality += sign * dot;
+        }
+        // SelectPenalty (equation 18.32), nonlinear.cc:112-119, 484-490
+        if (!prob.equality_constraints.empty() && q.lagrange_multipliers) {
+          const double new_penalty = q.lagrange_multipliers->l_infinity;
+          if (new_penalty > s.penalty) s.penalty = new_penalty * params.equality_penalty_scale_factor;
+        }
+        std::vector<LineSearchStep> steps;
+        const StepSizeSelectionResult step = SelectStepSize(prob, params, s.x, s.dx, s.errors_pre, dd, s.penalty, retraction,
+                                                            &s.cand, &steps);
+        const double old_lambda = s.lambda;
+        const OptimizerState old_state = s.state;
+        const std::optional<NLSTerminationState> maybe_exit =
+            UpdateLambdaAndCheckExitConditions(params, step, s.errors_pre, s.penalty, steps, &s.lambda, &s.state, &s.x, &s.cand);
+        out[i].iterations.push_back(NLSIteration{iter, old_state, old_lambda, s.errors_pre, q.termination_state,
+                                                 q.num_iterations, dd, s.penalty, step, std::move(steps)});
+        if (maybe_exit) {
+          out[i].termination_state = *maybe_exit;
+          s.done = true;
+        }
+      }
+    }
+    for (std::size_t i = 0; i < B; ++i) out[i].variables = st[i].x;  // not done: MAX_ITERATIONS (the default)
+    return out;
+  }
+
+ private:
+  static void CheckParams(const Params& p) {  // nonlinear.cc:49-73
+    const bool ok = p.max_iterations >= 0 && p.max_qp_iterations >= 1 && p.termination_kkt_tolerance > 0 &&
+                    p.absolute_exit_tol > 0 && p.relative_exit_tol >= 0 && p.relative_exit_tol <= 1 &&
+                    p.absolute_first_derivative_tol >= 0 && p.max_line_search_iterations >= 0 &&
+                    p.armijo_search_tau > 0 && p.armijo_search_tau < 1 && p.equality_penalty_initial > 0 &&
+                    p.lambda_initial >= 0 && p.lambda_failure_init > 0 && p.max_lambda > 0 && p.min_lambda >= 0;
+    if (!ok) throw std::invalid_argument("invalid ConstrainedNonlinearLeastSquares::Params (nonlinear.cc:49-73)");
+  }
+
+  // nonlinear.cc:531-538
+  static std::optional<double> QuadraticApproxMinimum(double phi_0, double phi_prime_0, double alpha_0, double phi_alpha_0) {
+    const double numerator = phi_alpha_0 - phi_prime_0 * alpha_0 - phi_0;
+    if (phi_prime_0 > 0 || numerator <= 0) return std::nullopt;
+    return -phi_prime_0 * alpha_0 * alpha_0 / (2.0 * numerator);
+  }
+  // nonlinear.cc:563-578 (explicit inverse of the 2x2 system) and :594-605
+  static std::optional<double> CubicApproxMinimum(double phi_0, double phi_prime_0, double alpha_0, double phi_alpha_0,
+                                                  double alpha_1, double phi_alpha_1) {
+    const double a00 = alpha_0 * alpha_0 * alpha_0, a01 = alpha_0 * alpha_0, a10 = alpha_1 * alpha_1 * alpha_1,
+                 a11 = alpha_1 * alpha_1;
+    const double r0 = phi_alpha_0 - phi_0 - phi_prime_0 * alpha_0, r1 = phi_alpha_1 - phi_0 - phi_prime_0 * alpha_1;
+    const double det = a00 * a11 - a01 * a10;
+    const double a = (a11 * r0 - a01 * r1) / det, b = (-a10 * r0 + a00 * r1) / det;
+    const double arg_sqrt = b * b - 3 * a * phi_prime_0;
+    if (a == 0.0 || arg_sqrt < -1.0e-12) return std::nullopt;
+    return (-b + std::sqrt(std::max(arg_sqrt, 0.))) / (3 * a);
+  }
+
+  // nonlinear.cc:351-416 (armijo_c1 = 1e-4, :121)
+  static StepSizeSelectionResult SelectStepSize(const Problem& prob, const Params& params, const Vector& x, const Vector& dx,
+                                                const Errors& errors_pre, const DirectionalDerivatives& derivatives,
+                                                double penalty, const Retraction& retraction, Vector* cand,
+                                                std::vector<LineSearchStep>* steps) {
+    constexpr double armijo_c1 = 1.0e-4;
+    const double directional_derivative = derivatives.Total(penalty);
+    double alpha = 1;
+    for (int iter = 0; iter <= params.max_line_search_iterations; ++iter) {
+      if (params.line_search_strategy == LineSearchStrategy::POLYNOMIAL_APPROXIMATION) {
+        if (iter > 0) {
+          std::optional<double> new_alpha;
+          if (iter == 1) {
+            new_alpha = QuadraticApproxMinimum(errors_pre.Total(penalty), directional_derivative, steps->back().alpha,
+                                               steps->back().errors.Total(penalty));
+          } else {
+            const LineSearchStep& s2 = (*steps)[steps->size() - 2];
+            const LineSearchStep& s1 = steps->back();
+            new_alpha = CubicApproxMinimum(errors_pre.Total(penalty), directional_derivative, s2.alpha,
+                                           s2.errors.Total(penalty), s1.alpha, s1.errors.Total(penalty));
+          }
+          if (!new_alpha || !std::isfinite(*new_alpha) || *new_alpha <= 0.0 || *new_alpha >= alpha)
+            return StepSizeSelectionResult::FAILURE_INVALID_ALPHA;
+          alpha = *new_alpha;
+        }
+      } else if (iter > 0) {
+        alpha = alpha * params.armijo_search_tau;
+      }
+      *cand = x;  // RetractCandidateVars, nonlinear.cc:160-168
+      if (retraction) retraction(*cand, dx, alpha);
+      else for (int j = 0; j < cand->rows(); ++j) (*cand)[j] += dx[j] * alpha;
+      const Errors errors_step = EvaluateNonlinearErrors(prob, *cand);
+      steps->push_back(LineSearchStep{alpha, errors_step});
+      if (errors_step.ContainsInvalidValues()) return StepSizeSelectionResult::FAILURE_NON_FINITE_COST;
+      if (derivatives.LInfinity() < params.absolute_first_derivative_tol) return StepSizeSelectionResult::FIRST_ORDER_SATISFIED;
+      if (directional_derivative > 0) return StepSizeSelectionResult::POSITIVE_DERIVATIVE;
+      if (errors_step.Total(penalty) <= errors_pre.Total(penalty) + directional_derivative * alpha * armijo_c1)
+        return StepSizeSelectionResult::SUCCESS;
+    }
+    return StepSizeSelectionResult::MAX_ITERATIONS;
+  }
+
+  // nonlinear.cc:296-343
+  static std::optional<NLSTerminationState> UpdateLambdaAndCheckExitConditions(
+      const Params& params, StepSizeSelectionResult step_result, const Errors& initial_errors, double penalty,
+      const std::vector<LineSearchStep>& steps, double* lambda, OptimizerState* state, Vector* x, Vector* cand) {
+    if (step_result == StepSizeSelectionResult::SUCCESS) {
+      x->swap(*cand);
+      if (*state == OptimizerState::ATTEMPTING_RESTORE_LM) *lambda = std::max(*lambda * params.lambda_decrease_on_restore, params.min_lambda);
+      else *lambda = std::max(*lambda * params.lambda_decrease_on_success, params.min_lambda);
+      *state = OptimizerState::NOMINAL;
+      const LineSearchStep& final_step = steps.back();
+      if (final_step.errors.LInfinity() < params.absolute_exit_tol) return NLSTerminationState::SATISFIED_ABSOLUTE_TOL;
+      if (final_step.errors.Total(penalty) > initial_errors.Total(penalty) * (1 - params.relative_exit_tol))
+        return NLSTerminationState::SATISFIED_RELATIVE_TOL;
+    } else if (step_result == StepSizeSelectionResult::FIRST_ORDER_SATISFIED) {
+      return NLSTerminationState::SATISFIED_FIRST_ORDER_TOL;
+    } else if (step_result == StepSizeSelectionResult::MAX_ITERATIONS ||
+               step_result == StepSizeSelectionResult::POSITIVE_DERIVATIVE) {
+      if (*state == OptimizerState::NOMINAL) {
+        *lambda = std::max(params.lambda_failure_init, *lambda * 10.0);
+        *state = OptimizerState::ATTEMPTING_RESTORE_LM;
+      } else {
+        *lambda *= 10.0;
+      }
+      if (*lambda > params.max_lambda) return NLSTerminationState::MAX_LAMBDA;
+    }
+    return std::nullopt;
+  }
+
+  const Problem* p_;
+  Retraction custom_retraction_;
+  Vector variables_;
+};
+
+}  // namespace mini_opt_b200
