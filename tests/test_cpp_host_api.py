@@ -36,3 +36,11 @@ def test_cpp_nls_host_api_cpu(tmp_path):
     """Residual / LinearizeAndFillQP / EvaluateNonlinearErrors of nonlinear.hpp (no device calls)."""
     r = subprocess.run([str(build(tmp_path, "test_nls_host_api")), "cpu"], capture_output=True, text=True)
     assert r.returncode == 0 and "cpu ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_nls_host_api_gpu(tmp_path):
+    """The reference's own nonlinear test problems (test/nonlinear_test.cc) through
+    ConstrainedNonlinearLeastSquares::SolveBatch: host Residual callbacks, batched QP solves on the device."""
+    r = subprocess.run([str(build(tmp_path, "test_nls_host_api")), "gpu"], capture_output=True, text=True)
+    assert r.returncode == 0 and "gpu ok" in r.stdout, r.stdout + r.stderr
