@@ -34,6 +34,16 @@ static std::array<double, 1> ProductExpression(const std::array<double, 2>& x, d
   return {x[0] * x[1] - v};
 }
 
+// one line per start point in the format of oracle/ref_nls_host_golden.cc (compared by tests/test_cpp_host_api.py)
+static void PrintResults(const char* name, const std::vector<NLSSolverOutputs>& out) {
+  for (std::size_t i = 0; i < out.size(); ++i) {
+    int qp_iters = 0;
+    for (const NLSIteration& it : out[i].iterations) qp_iters += it.qp_iterations;
+    std::printf("RESULT %s %zu %d %zu %d %.17g %.17g\n", name, i, static_cast<int>(out[i].termination_state),
+                out[i].iterations.size(), qp_iters, out[i].variables[0], out[i].variables[1]);
+  }
+}
+
 static bool SatisfiedTol(NLSTerminationState s) {  // structs.hpp:243-248
   return s == NLSTerminationState::SATISFIED_ABSOLUTE_TOL || s == NLSTerminationState::SATISFIED_RELATIVE_TOL ||
          s == NLSTerminationState::SATISFIED_FIRST_ORDER_TOL;
@@ -80,6 +90,7 @@ static void TestRosenbrock(bool lm) {  // nonlinear_test.cc:391-460
   const std::vector<Vector> guesses = {{-5, -3}, {10, 8}, {-20, 3}, {0, -5}, {4, 0}, {100, 50}, {-35, 40}, {1000, -50}, {0.8, -0.3}};
   const std::vector<const Problem*> problems(guesses.size(), &problem);
   const std::vector<NLSSolverOutputs> out = ConstrainedNonlinearLeastSquares::SolveBatch(problems, p, guesses);
+  PrintResults(lm ? "rosenbrock_lm" : "rosenbrock", out);
   for (std::size_t i = 0; i < out.size(); ++i) {
     CHECK(out[i].termination_state == NLSTerminationState::SATISFIED_ABSOLUTE_TOL);
     int qp_iters = 0;
@@ -106,6 +117,7 @@ static void TestInequalityConstrainedRosenbrock() {  // nonlinear_test.cc:463-50
   const std::vector<Vector> guesses = {{12, -5}, {100.0, -20.0}, {1423.0, -400.0}, {-20.0, 10.0}, {-120.0, 35.0}, {-50.0, 0.5}};
   const std::vector<const Problem*> problems(guesses.size(), &problem);
   const std::vector<NLSSolverOutputs> out = ConstrainedNonlinearLeastSquares::SolveBatch(problems, p, guesses);
+  PrintResults("rosenbrock_ineq", out);
   for (const NLSSolverOutputs& o : out) {
     CHECK(o.termination_state != NLSTerminationState::MAX_ITERATIONS && o.termination_state != NLSTerminationState::MAX_LAMBDA);
     CHECK(std::abs(o.variables[0] - 1.2) < 1e-6 && std::abs(o.variables[1] - 0.5) < 1e-6);
