@@ -375,3 +375,32 @@ def test_dmma_kernel_variants_agree(dev, monkeypatch, n, k, B, guess):
         assert same.mean() >= (1.0 if guess == abi.MO_GUESS_NAIVE else 0.97), (name, same.mean())
         rel = np.abs(got.vars[:, :n] - ref.vars[:, :n]).max(axis=1) / np.maximum(1.0, np.abs(ref.vars[:, :n]).max(axis=1))
         assert rel[same].max() < 1e-9, (name, rel[same].max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dmma_variant", ["warp", "cta"], indirect=True)
+@pytest.mark.parametrize("n,k", [(64, 16), (32, 8), (16, 8)])
+def test_dmma_kernels_log_and_user_guess_vs_oracle(dev, oracle, n, k, dmma_variant):
+    """The corners of the DMMA kernels that the golden box batches do not reach: the per-iteration log
+    (QPInteriorPointIteration rows: kkt_initial, kkt_final, mu, alpha) and USER_PROVIDED start points with
+    initialize_mu_with_complementarity, both against the CPU oracle on the same inputs."""
+    m, B = 2 * n, 256
+    arrs = synth.box_qp_batch_numpy(n, k, B, seed=21, explicit_constraints=False)
+    prm = synth.solve_params(abi.MO_GUESS_NAIVE)
+    ref, _ = oracle.qp_solve("oracle", arrs, prm, log=True)
+    out = gpu_solve(arrs, prm, dev, log=True)
+    compare(out, ref, n)
+    for p in range(0, B, 13):
+        its = int(out.iters[p])
+        assert_log_close(out.iter_log[p, :its], ref.iter_log[p, :its])
+    rng = np.random.default_rng(3)
+    uv = np.zeros((B, abi.vars_stride(n, k, m)))
+    uv[:, :n] = rng.uniform(-0.5, 0.5, (B, n))
+    uv[:, n:n + m] = rng.uniform(0.1, 1.0, (B, m))
+    uv[:, n + m:n + m + k] = rng.uniform(-1, 1, (B, k))
+    uv[:, n + m + k:] = rng.uniform(0.1, 1.0, (B, m))
+    prm = synth.solve_params(abi.MO_GUESS_USER_PROVIDED)
+    prm.initialize_mu_with_complementarity = True
+    ref, _ = oracle.qp_solve("oracle", arrs, prm, user_vars=uv)
+    out = gpu_solve(arrs, prm, dev, user_vars=uv)
+    compare(out, ref, n, min_same=0.99, min_x=0.99)
