@@ -419,7 +419,9 @@ __host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost,
 
 // ConstrainedNonlinearLeastSquares::Solve (nonlinear.cc:75-158), one warp (= one 32-thread block) per problem.
 #ifndef MO_IK_MINB
-#define MO_IK_MINB 24  // measured on B200 (6 links, 100K problems): 8 -> 769 ms, 16 -> 672, 24 -> 641, 32 -> 682
+// resident warps per SM; measured on B200 with the ticket queue, 100K problems (6 links / 12 links, problems/s):
+// 12 -> 700K / 229K, 16 -> 787K / 229K, 24 -> 802K / 203K (80 registers: spills at n = 12), 32 -> 794K / 179K
+#define MO_IK_MINB 16
 #endif
 constexpr int kIkTicketSlots = 64;  // launches in flight that may hold a ticket counter at the same time
 __device__ unsigned long long g_ik_tickets[kIkTicketSlots];
