@@ -10,14 +10,15 @@
 // Why a second DMMA kernel next to qp_dm_kernel (CTA per problem, matrix in accumulator registers AND L in shared
 // memory): one factorization is a chain of p dependent pivots (~150-200 cycles each), so a CTA-per-problem kernel is
 // bound by that latency times the number of co-resident problems, and two on-chip copies of the matrix cap residency
-// at 4 problems per SM (n = 64). Here a problem costs one warp and ONE copy of the matrix (33 KB at n = 64, 10 KB at
-// n = 32): 6 resp. 18+ independent problems per SM, no CTA barriers, and the pivot chains of different problems
-// overlap.
+// at 4 problems per SM (n = 64). Here a problem costs one warp and ONE copy of the matrix (28 KB at n = 64, 10 KB at
+// n = 32): 7 resp. 12 independent problems per SM (shared memory resp. a spill-free register budget), no CTA barriers,
+// and the pivot chains of different problems overlap.
 //
 // Layout: tile (I, J), I >= J, 64 doubles, element [r][c] at wd_el(r, c) = (c >> 2) * 32 + r' * 4 + (c & 3) with r' = r
 // (first half) or r ^ 2 (second half): lane l = 4 r + q of a warp reads [r][4h + q] at l resp. 32 + (l ^ 8) -- which is at once the DMMA A fragment of the tile and the B fragment of its
-// transpose, 256 contiguous bytes, bank-conflict free. Tile row NT (one past the matrix) carries the right-hand side
-// in its row 0, so the forward substitution and the D^-1 scaling fall out of the panel solve.
+// transpose, 256 contiguous bytes, bank-conflict free. For n <= 32 tile row NT (one past the matrix) carries the
+// right-hand side in its row 0, so the forward substitution and the D^-1 scaling fall out of the panel solve; at n = 64
+// the rhs stays out of the tile array (WdLayout::RHS_ROW, wd_forward_block).
 #pragma once
 #include <cstdio>
 #include "qp_dmma.cuh"
