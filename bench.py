@@ -377,9 +377,9 @@ def main():
     # ncu dram__bytes_read.sum + dram__bytes_write.sum per pass of the default workload (profiles/r01_tpp_n8_ncu_full_summary.txt:
     # guess kernel 0.894 + 0.328 GB, iterate kernel 1.247 + 0.364 GB); other shapes: not captured -> null
     # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from `ncu --set full`, scaled to this launch:
-    # n=8: profiles/r01_tpp_n8_ncu_full_summary.txt; n=64: profiles/r01_wd64_ncu_full_summary.txt (161.7 + 10.2 MB / 5328 QPs,
+    # n=8: profiles/r01_tpp_n8_ncu_full_summary.txt; n=64: profiles/r01_wd64_ncu_full_summary.txt (188.7 + 12.4 MB / 6216 QPs,
     # below the algorithmic bytes because only the lower block triangle of G is fetched; re-reads per Newton step hit L2)
-    traffic = {(8, 2, 1 << 20): 2.833e9, (64, 16, 65536): 171.89e6 / 5328 * 65536}.get((n, k, B))
+    traffic = {(8, 2, 1 << 20): 2.833e9, (64, 16, 65536): 201.06e6 / 6216 * 65536}.get((n, k, B))
     roofline = {
         "bound": "tensor", "pipe": "fp64: DFMA and DMMA.8x8x4 share one 64 FMA/clk/SM datapath (profiles/r01_dmma_vs_dfma_microbench.txt)",
         "traffic": traffic, "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak,
