@@ -2,15 +2,21 @@
 """Benchmark of the hot path: batched interior point QP solves (BASELINE config 2 by default).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 8 --k 2 --batch 1048576]
+  python bench.py --sweep            # BASELINE config 5: one JSON line per (n, batch), at the --gpus given
+  python bench.py --workload ik      # BASELINE config 3 as the main line
 
 A "step" is one pass of mo_qp_ip_solve_batch over one synthetic batch (SURVEY 8(d) recipe) of `--batch`
 box-constrained QPs per GPU. Metric: IP Newton steps/s (sum of per-problem iteration counts / time), whole job.
   value     inputs resident in HBM, device time by CUDA events on the launch stream, max over ranks
   e2e       same batch through mo_qp_ip_solve_batch_host from PINNED HOST buffers (H2D + solve + D2H inside)
-  roofline  algorithmic FP64 flops per launch (F(n,k,m) per Newton step) / kernel time, against an
-            FP64 DFMA peak measured live on this GPU (MEASURED_PEAKS.json has no FP64 entry), plus the HBM view
-  cpu_baseline  the reference's own QPInteriorPointSolver (oracle/_ref, unmodified sources) one solver per
-            thread on all host cores, bounded sample of the same workload (rank 0, N=1 only)
+  roofline  algorithmic FP64 flops per launch (F(n,k,m) per Newton step) / kernel time, against the
+            FP64 peak measured live on this GPU: the DFMA peak for the n = 8 kernels, the DMMA.8x8x4 peak for the kernels
+            whose O(p^3) work runs on DMMA (MEASURED_PEAKS.json has no FP64 entry), plus the HBM view
+  cpu_baseline  the reference's own QPInteriorPointSolver (oracle/_ref, unmodified sources), one solver per std::thread
+            on all host cores, on the FIRST `--cpu-sample` problems of the GPU's own batch (rank 0, N=1 only)
+  parity    GPU results vs the reference's on those same bytes: identical status / iteration count fractions, x to 1e-9
+  also      the same record for BASELINE config 4 (64K QPs n=64, DMMA kernel) and config 3 (100K 6-link chain IK),
+            measured in the same process after the main line
 `--impl reference` times that CPU implementation alone (rank 0) and prints the same JSON shape.
 Multi-GPU: the batch shards by rank with no collective on the solve path (weak scaling: per-GPU batch fixed).
 """
@@ -29,6 +35,7 @@ import numpy as np
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tools"))
 
 from mini_opt_b200 import abi, synth  # noqa: E402
 
@@ -94,23 +101,72 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def run_reference_cpu(n, k, sample, threads, seed=1234, repeats=1):
-    """Time the UNMODIFIED reference (oracle/_ref) on `sample` problems with `threads` host threads."""
-    from oracle import oracle_py as O  # the one place bench.py touches oracle/: CPU baseline / reference arm
+class Ctx:
+    """Rank / device plumbing shared by the workloads (torch = device memory, streams, torch.distributed only)."""
+
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        self.dev = None
+
+    def init_gpu(self):
+        torch = self.torch
+        assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+        from mini_opt_b200 import lib
+        self.lib = lib
+        self.L = lib.load()
+        self.peaks = {}
+        try:
+            self.peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        self.dfma_peak = lib.measure_fp64_peak(self.local)
+        self.dmma_peak = lib.measure_dmma_peak(self.local)
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def reduce(self, vals, op):
+        """all-reduce a list of python floats (MAX or SUM) over ranks: timing scalars only, never problem data."""
+        if self.dist is None:
+            return list(vals)
+        t = self.torch.tensor(list(vals), dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return [float(v) for v in t]
+
+    def finish(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def gen_qp_batch(n, k, batch, seed, dev):
+    """The synthetic batch of SURVEY 8(d). Generated on the device when there is one (bench: straight into HBM; the
+    reference arm copies it back so both arms see the same stream), else with numpy."""
+    if dev is not None:
+        return synth.box_qp_batch_torch(n, k, batch, seed=seed, device=dev)
+    return synth.box_qp_batch_numpy(n, k, batch, seed=seed, explicit_constraints=False)
+
+
+def run_reference_qp(arrs_host, prm, threads):
+    """Time the UNMODIFIED reference (oracle/_ref) on a host batch. The timed region is the threaded solve only:
+    unpacking the flat arrays into mini_opt::QP objects and allocating outputs happen before it (BASELINE.md 4)."""
+    from oracle import oracle_py as O  # bench.py touches oracle/ only here: CPU baseline / reference arm / parity checker
     kind = "reference" if O.REF_SO.exists() else "port"
-    arrs = synth.box_qp_batch_numpy(n, k, sample, seed=seed, explicit_constraints=False)
-    prm = synth.solve_params()
-    best, steps, solved = None, 0, 0
-    for _ in range(repeats):
-        t0 = time.perf_counter()
-        out, steps = O.qp_solve("ref" if kind == "reference" else "oracle", arrs, prm,
-                                nthreads=threads if kind == "reference" else 1)
-        dt = time.perf_counter() - t0
-        solved = int((out.status == 0).sum())
-        best = dt if best is None or dt < best else best
-    return dict(kind=kind, seconds=best, steps=steps, solved=solved, cores=threads if kind == "reference" else 1,
-                sample=f"{sample} QPs n={n} k={k} m={2 * n} (same recipe, seed {seed}), "
-                       f"{'one QPInteriorPointSolver per std::thread' if kind == 'reference' else 'scalar C port'}")
+    out, steps, seconds = O.qp_solve_timed("ref" if kind == "reference" else "oracle", arrs_host, prm,
+                                           nthreads=threads if kind == "reference" else 1)
+    return dict(kind=kind, seconds=seconds, steps=steps, solved=int((out.status == 0).sum()), out=out,
+                cores=threads if kind == "reference" else 1)
 
 
 def pinned_copy(L, arr):
@@ -125,160 +181,339 @@ def pinned_copy(L, arr):
     return view, ptr
 
 
-def reference_arm(args, rank, world):
-    """--impl reference: the reference's CPU implementation, all host threads, bounded sample per step."""
-    if rank != 0:
-        return
-    threads = host_cores()
-    sample = args.cpu_sample
-    run_reference_cpu(args.n, args.k, min(sample, 4096), threads)  # page-in / thread start
-    times, steps_per = [], 0
-    res = None
-    for i in range(args.warmup + args.steps):
-        res = run_reference_cpu(args.n, args.k, sample, threads, seed=1234 + i)
-        if i >= args.warmup:
-            times.append(res["seconds"])
-            steps_per += res["steps"]
-    total = sum(times)
-    value = steps_per / total
-    line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args), "n": args.n, "k": args.k, "m": 2 * args.n,
-                   "cpu_sample_per_step": sample, "timing": "host wall clock around the threaded solve"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": res["cores"], "kind": res["kind"],
-                         "sample": res["sample"]},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+def qp_workload_name(n, k, B):
+    return (f"{'config2' if n == 8 else 'config4' if n == 64 else 'config5'}-like: {B} box-constrained QPs per GPU, "
+            f"n={n}, k={k}, m={2 * n}, SOLVE_EQUALITY_CONSTRAINED guess, sigma=0.1, kkt_tol=1e-9, max 30 iterations")
+
+
+def traffic_record(kernel, n, k):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel per QP, from the committed `ncu --set full`
+    capture named in profiles/traffic.json (source file and commit are recorded there, not hard-coded here)."""
+    try:
+        tab = json.loads((ROOT / "profiles" / "traffic.json").read_text())
+        return tab.get(f"{kernel}:{n}:{k}")
+    except Exception:
+        return None
+
+
+def qp_pass(ctx: Ctx, n, k, B, steps, warmup, with_e2e=True, cpu_sample=0, seed=1234):
+    """One measured workload: device-resident value, roofline, e2e, and (N=1, rank 0) cpu_baseline + parity."""
+    import parity as par
+    torch, dev, lib, L = ctx.torch, ctx.dev, ctx.lib, ctx.L
+    from mini_opt_b200 import qp
+    m = 2 * n
+    prm = synth.solve_params()
+    arrs = gen_qp_batch(n, k, B, seed + ctx.rank, dev)
+    out = qp.alloc_out_torch(B, n, k, m, dev, lagrange=False)
+    stream = torch.cuda.current_stream(dev)
+
+    def step():
+        qp.solve_batch_device(arrs, prm, out, dev, stream)
+
+    warmup = max(warmup, 3)
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    launches0 = lib.launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    ctx.barrier()
+    torch.cuda.synchronize()
+    with ClockSampler(ctx.local) as clocks:
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record(stream)
+        for a, b in evs:
+            a.record(stream)
+            step()
+            b.record(stream)
+        t1.record(stream)
+        torch.cuda.synchronize()
+    ctx.barrier()
+    launches = lib.launch_count() - launches0
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    steps_local = int(out.iters.sum().item())
+    solved_local = int((out.status == 0).sum().item())
+    total_ms = ctx.reduce([t0.elapsed_time(t1)], "max")[0]
+    newton_steps, solved = ctx.reduce([float(steps_local), float(solved_local)], "sum")
+    sec_per_step = total_ms * 1e-3 / steps
+    value = newton_steps / sec_per_step
+
+    # roofline of the dominant kernel on this rank
+    F = flops_per_step(n, k, m)
+    tflops = F * steps_local / (kernel_ms * 1e-3) / 1e12
+    alg_bytes = algorithmic_bytes_per_qp(n, k, m) * B
+    hbm_peak = float(ctx.peaks.get("hbm_gbs", 6650.0))
+    variant = lib.kernel_variant(n, k, m, arrs.flags)
+    dmma = variant.startswith("dmma")
+    peak = ctx.dmma_peak if dmma else ctx.dfma_peak
+    tr = traffic_record(variant, n, k)
+    roofline = {
+        "bound": "tensor",
+        "pipe": ("fp64 tensor path: mma.sync.m8n8k4.f64 = DMMA.8x8x4" if dmma else "fp64 DFMA (no 8x8x4 contraction at this size)"),
+        "traffic": (tr["bytes_per_qp"] * B if tr else None), "traffic_source": (tr["source"] if tr else None),
+        "achieved": tflops, "peak": peak, "unit": "TFLOP/s", "frac": tflops / peak,
+        "kernel": variant, "kernel_ms": kernel_ms, "flops_per_newton_step": F, "newton_steps_per_launch": steps_local,
+        "peak_source": ("DMMA.8x8x4" if dmma else "DFMA") + " microbenchmark measured live on this GPU "
+                       "(mo_measure_dmma_peak / mo_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
+        "dfma_peak": ctx.dfma_peak, "dmma_peak": ctx.dmma_peak,
+        "hbm": {"achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
+                "peak_source": "MEASURED_PEAKS.json" if ctx.peaks else "fallback"},
     }
-    print(json.dumps(line), flush=True)
+
+    # e2e: pinned host buffers through the host entry point (H2D + solve + D2H inside the timed region)
+    e2e = None
+    if with_e2e:
+        host = synth.to_numpy(arrs)
+        keep = []
+
+        def pin(a):
+            v, p = pinned_copy(L, a)
+            keep.append(p)
+            return v
+        harrs = abi.QPBatchArrays(n=n, k=k, m=m, batch=B, G=pin(host.G), c=pin(host.c), A_eq=pin(host.A_eq) if k else None,
+                                  b_eq=pin(host.b_eq) if k else None, ineq_b=pin(host.ineq_b), flags=host.flags)
+        hout = abi.QPOutArrays(vars=pin(np.zeros((B, n + 2 * m + k))), status=pin(np.zeros(B, dtype=np.int32)),
+                               iters=pin(np.zeros(B, dtype=np.int32)), kkt_final=pin(np.zeros((B, 4))))
+        h2d = sum(a.nbytes for a in (harrs.G, harrs.c, harrs.A_eq, harrs.b_eq, harrs.ineq_b) if a is not None)
+        d2h = hout.vars.nbytes + hout.status.nbytes + hout.iters.nbytes + hout.kkt_final.nbytes
+        for _ in range(2):
+            qp.solve_batch_host(harrs, prm, hout, ctx.local)
+        ctx.barrier()
+        torch.cuda.synchronize()
+        t_start = time.perf_counter()
+        e2e_steps = max(3, min(steps, 5))
+        for _ in range(e2e_steps):
+            qp.solve_batch_host(harrs, prm, hout, ctx.local)
+        torch.cuda.synchronize()
+        e2e_sec = ctx.reduce([(time.perf_counter() - t_start) / e2e_steps], "max")[0]
+        assert np.array_equal(hout.iters, out.iters.cpu().numpy()), "host entry point disagrees with device path"
+        e2e = {"value": newton_steps / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * ctx.world,
+               "d2h_bytes_per_step": int(d2h) * ctx.world, "ms_per_step": 1e3 * e2e_sec,
+               "qps_per_sec": B * ctx.world / e2e_sec}
+        for p in keep:
+            L.mo_host_free(p)
+
+    # cpu_baseline + parity: the reference on the first cpu_sample problems of THIS batch (same bytes)
+    cpu, parity = None, None
+    if ctx.rank == 0 and ctx.world == 1 and cpu_sample > 0:
+        S = min(cpu_sample, B)
+        threads = host_cores()
+        sample = synth.to_numpy(arrs, 0, S)
+        run_reference_qp(synth.to_numpy(arrs, 0, min(S, 2048)), prm, threads)  # page-in / thread start
+        r = run_reference_qp(sample, prm, threads)
+        cpu = {"value": r["steps"] / r["seconds"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+               "sample": f"first {S} QPs of the GPU's own batch (n={n} k={k} m={m}, same bytes), "
+                         f"{'one QPInteriorPointSolver per std::thread, solve loop only' if r['kind'] == 'reference' else 'scalar C port'}, "
+                         "g++ -O2 -march=x86-64-v3 (prebuilt in the CPU container; /root/reference is absent on the GPU box)",
+               "qps_per_sec": r["solved"] / r["seconds"], "seconds": r["seconds"]}
+        got = abi.QPOutArrays(vars=out.vars[:S].cpu().numpy(), status=out.status[:S].cpu().numpy(),
+                              iters=out.iters[:S].cpu().numpy(), kkt_final=out.kkt_final[:S].cpu().numpy())
+        parity = par.compare_qp(got, r["out"], n, par.clamped_start_mask(sample, prm.initial_guess_method))
+        parity["against"] = r["kind"]
+
+    return {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ctx.world, "steps": steps, "warmup": warmup,
+        "ms_per_step": 1e3 * sec_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": qp_workload_name(n, k, B), "n": n, "k": k, "m": m, "batch_per_gpu": B,
+                   "l2": "inputs (%.0f MB per pass) %s the 126 MB L2" % (alg_bytes / 1e6, "exceed" if alg_bytes > 126e6 else "fit in"),
+                   "newton_steps_per_qp": newton_steps / (B * ctx.world)},
+        "solved_qps_per_sec": solved / sec_per_step, "converged_fraction": solved / (B * ctx.world),
+        "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clocks.summary(),
+    }
 
 
-def workload_name(args):
-    return (f"config2-like: {args.batch} box-constrained QPs per GPU, n={args.n}, k={args.k}, m={2 * args.n}, "
-            f"SOLVE_EQUALITY_CONSTRAINED guess, sigma=0.1, kkt_tol=1e-9, max 30 iterations")
-
-
-def ik_main(args, rank, world, local):
+def ik_pass(ctx: Ctx, links, B, steps, warmup, with_e2e=True, cpu_sample=0):
     """BASELINE config 3: batch of transform-chain IK problems through mo_nls_solve_chain_ik_batch (device SQP + LM loop).
     Metric: IP Newton steps/s inside the NLS solves (sum of QP iterations / time) and NLS problems/s."""
-    import torch
-    import torch.distributed as dist
-    from mini_opt_b200 import lib, nls
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    lib.load()
-    B = args.batch if args.batch != (1 << 20) else 100000
+    import parity as par
+    torch, dev, lib = ctx.torch, ctx.dev, ctx.lib
+    from mini_opt_b200 import nls
     prm = synth.chain_ik_params()
-    if args.impl == "reference":
-        if rank == 0:
-            from oracle import oracle_py as O
-            sample = min(B, 20000)
-            ch = synth.chain_ik_batch_numpy(args.links, sample, seed=4321)
-            threads = host_cores()
-            O.nls_solve_chain("ref", synth.chain_ik_batch_numpy(args.links, 512, seed=1), prm, nthreads=threads)
-            t0 = time.perf_counter()
-            out, total = O.nls_solve_chain("ref", ch, prm, nthreads=threads)
-            dt = time.perf_counter() - t0
-            print(json.dumps({"impl": "reference", "metric": METRIC, "value": total / dt, "unit": UNIT, "n_gpus": args.gpus,
-                              "steps": 1, "warmup": 0, "ms_per_step": 1e3 * dt, "higher_is_better": True, "scaling": "weak",
-                              "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                              "config": {"workload": f"config3: {sample} chain-IK problems, {args.links} links (CPU sample)"},
-                              "nls_problems_per_sec": sample / dt,
-                              "cpu_baseline": {"value": total / dt, "unit": UNIT, "cores": threads, "kind": "reference",
-                                               "sample": f"{sample} problems, one ConstrainedNonlinearLeastSquares per std::thread"},
-                              "e2e": {"value": total / dt, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                              "gpu_launches": 0}), flush=True)
-        return
-    ch = nls.chain_to_device(synth.chain_ik_batch_numpy(args.links, B, seed=4321 + rank), dev)
+    host_ch = synth.chain_ik_batch_numpy(links, B, seed=4321 + ctx.rank)
+    ch = nls.chain_to_device(host_ch, dev)
     out = nls.alloc_nls_out_torch(B, ch.n, dev)
     stream = torch.cuda.current_stream(dev)
-    for _ in range(max(args.warmup, 3)):
+    warmup = max(warmup, 3)
+    for _ in range(warmup):
         nls.solve_chain_ik_device(ch, prm, out, dev, stream)
     torch.cuda.synchronize()
     l0 = lib.launch_count()
-    if world > 1:
-        dist.barrier()
+    ctx.barrier()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
+    with ClockSampler(ctx.local) as clocks:
         t0.record(stream)
-        for _ in range(args.steps):
+        for _ in range(steps):
             nls.solve_chain_ik_device(ch, prm, out, dev, stream)
         t1.record(stream)
         torch.cuda.synchronize()
-    ms = t0.elapsed_time(t1) / args.steps
-    qp_steps = float(out.qp_iterations.sum().item())
-    ok = float((out.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL).sum().item())
-    stats = torch.tensor([ms, qp_steps, ok], dtype=torch.float64, device=dev)
-    if world > 1:
-        mx, sm_ = stats.clone(), stats.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        dist.all_reduce(sm_, op=dist.ReduceOp.SUM)
-        ms, qp_steps, ok = float(mx[0]), float(sm_[1]), float(sm_[2])
+    launches = lib.launch_count() - l0
+    ms_local = t0.elapsed_time(t1) / steps
+    qp_local = float(out.qp_iterations.sum().item())
+    ok_local = float((out.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL).sum().item())
     nls_iters = float(out.iterations.sum().item())
     # algorithmic flops (SURVEY 8(d)): F(n, k, m) per inner Newton step + per outer iteration the chain FK / Jacobians
     # (~300 per link) and the linearization R N (N + 1) + 2 R N + N with R = cost rows
     n_, m_, R_ = ch.n, ch.m, ch.n_cost
-    flops_local = qp_steps * flops_per_step(n_, ch.n_eq, m_) + nls_iters * (300.0 * args.links + R_ * n_ * (n_ + 1) + 2 * R_ * n_ + n_)
-    fl = torch.tensor([flops_local], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(fl, op=dist.ReduceOp.SUM)
-    fp64_peak = lib.measure_fp64_peak(local)
+    flops_local = qp_local * flops_per_step(n_, ch.n_eq, m_) + nls_iters * (300.0 * links + R_ * n_ * (n_ + 1) + 2 * R_ * n_ + n_)
+    ms = ctx.reduce([ms_local], "max")[0]
+    qp_steps, ok, flops = ctx.reduce([qp_local, ok_local, flops_local], "sum")
     e2e = None
-    if not args.no_e2e:
-        pipe = nls.ChainIKHostPipeline(synth.chain_ik_batch_numpy(args.links, B, seed=4321 + rank), dev)
+    if with_e2e:
+        pipe = nls.ChainIKHostPipeline(host_ch, dev)
         for _ in range(2):
             pipe.solve(prm)
-        if world > 1:
-            dist.barrier()
+        ctx.barrier()
         torch.cuda.synchronize()
-        n_e2e = max(2, min(args.steps, 3))
+        n_e2e = max(2, min(steps, 3))
         ts = time.perf_counter()
         for _ in range(n_e2e):
             hres = pipe.solve(prm)
-        sec = (time.perf_counter() - ts) / n_e2e
+        sec = ctx.reduce([(time.perf_counter() - ts) / n_e2e], "max")[0]
         assert int(hres["qp_iterations"].sum()) == int(out.qp_iterations.sum().item()), "host pipeline disagrees with device path"
-        tsec = torch.tensor([sec], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(tsec, op=dist.ReduceOp.MAX)
-        e2e = {"value": qp_steps / float(tsec[0]), "unit": UNIT, "h2d_bytes_per_step": int(pipe.h2d_bytes) * world,
-               "d2h_bytes_per_step": int(pipe.d2h_bytes) * world, "ms_per_step": 1e3 * float(tsec[0]),
-               "nls_problems_per_sec": B * world / float(tsec[0])}
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        from oracle import oracle_py as O  # bench cpu_baseline leg: the unmodified reference, timed as the checker's twin
-        sample = min(B, 20000)
-        chs = synth.chain_ik_batch_numpy(args.links, sample, seed=4321)
+        e2e = {"value": qp_steps / sec, "unit": UNIT, "h2d_bytes_per_step": int(pipe.h2d_bytes) * ctx.world,
+               "d2h_bytes_per_step": int(pipe.d2h_bytes) * ctx.world, "ms_per_step": 1e3 * sec,
+               "nls_problems_per_sec": B * ctx.world / sec}
+    cpu, parity = None, None
+    if ctx.rank == 0 and ctx.world == 1 and cpu_sample > 0:
+        from oracle import oracle_py as O  # cpu_baseline leg: the unmodified reference, also the parity checker
+        S = min(B, cpu_sample)
+        chs = synth.chain_slice(host_ch, 0, S)
         threads = host_cores()
-        O.nls_solve_chain("ref", synth.chain_ik_batch_numpy(args.links, 512, seed=1), prm, nthreads=threads)
+        O.nls_solve_chain("ref", synth.chain_slice(host_ch, 0, min(S, 512)), prm, nthreads=threads)
         tc = time.perf_counter()
-        _, total = O.nls_solve_chain("ref", chs, prm, nthreads=threads)
+        ref, total = O.nls_solve_chain("ref", chs, prm, nthreads=threads)
         dtc = time.perf_counter() - tc
         cpu = {"value": total / dtc, "unit": UNIT, "cores": threads, "kind": "reference",
-               "sample": f"{sample} problems of the same recipe, one ConstrainedNonlinearLeastSquares per std::thread",
-               "nls_problems_per_sec": sample / dtc, "seconds": dtc}
-    if rank == 0:
-        tfl = float(fl[0]) / (ms * 1e-3) / 1e12
-        roofline = {"bound": "tensor", "pipe": "fp64 (DFMA; the n <= 12 systems have no 8x8x4 contraction for DMMA)",
-                    "achieved": tfl, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tfl / fp64_peak, "traffic": None,
-                    "kernel": "nls_chain_ik_kernel", "kernel_ms": ms,
-                    "algorithmic_flops_per_launch": float(fl[0]),
-                    "peak_source": "DFMA microbenchmark measured live on this GPU (mo_measure_fp64_peak)",
-                    "note": "one warp per problem, dependent scalar chains: latency-bound, see DESIGN.md 3.2"}
-        print(json.dumps({"roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                          "metric": METRIC, "value": qp_steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                          "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-                          "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                          "config": {"workload": f"config3: {B} transform-chain IK problems per GPU, {args.links} Z-revolute links, "
-                                                 "2 cost rows, joint limits +-pi/2, ARMIJO, max_qp_iterations=20, ModPi retraction",
-                                     "links": args.links, "batch_per_gpu": B},
-                          "nls_problems_per_sec": B * world / (ms * 1e-3), "absolute_tol_fraction": ok / (B * world),
-                          "gpu_launches": int(lib.launch_count() - l0), "clocks": clocks.summary()}), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+               "sample": f"first {S} problems of the GPU's own batch, one ConstrainedNonlinearLeastSquares per std::thread",
+               "nls_problems_per_sec": S / dtc, "seconds": dtc}
+        got = nls.nls_out_to_numpy(out)
+        got = abi.NLSOutArrays(**{f: getattr(got, f)[:S] for f in ("x", "termination", "iterations", "qp_iterations", "ls_steps", "errors")})
+        parity = par.compare_nls(got, ref)
+        parity["against"] = "reference"
+    tfl = flops / ctx.world / (ms * 1e-3) / 1e12
+    roofline = {"bound": "tensor", "pipe": "fp64 (DFMA; the n <= 12 systems have no 8x8x4 contraction for DMMA)",
+                "achieved": tfl, "peak": ctx.dfma_peak, "unit": "TFLOP/s", "frac": tfl / ctx.dfma_peak, "traffic": None,
+                "kernel": "nls_chain_ik_kernel", "kernel_ms": ms, "algorithmic_flops_per_launch": flops / ctx.world,
+                "peak_source": "DFMA microbenchmark measured live on this GPU (mo_measure_fp64_peak)",
+                "note": "one warp per problem, dependent scalar chains: latency-bound, see DESIGN.md 3.2"}
+    return {"metric": METRIC, "value": qp_steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ctx.world, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"config3: {B} transform-chain IK problems per GPU, {links} Z-revolute links, "
+                                   "2 cost rows, joint limits +-pi/2, ARMIJO, max_qp_iterations=20, ModPi retraction",
+                       "links": links, "batch_per_gpu": B},
+            "nls_problems_per_sec": B * ctx.world / (ms * 1e-3), "absolute_tol_fraction": ok / (B * ctx.world),
+            "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "e2e": e2e,
+            "gpu_launches": int(launches), "clocks": clocks.summary()}
+
+
+ALSO_KEYS = ("value", "unit", "ms_per_step", "config", "roofline", "e2e", "parity", "cpu_baseline", "converged_fraction",
+             "solved_qps_per_sec", "nls_problems_per_sec", "absolute_tol_fraction", "gpu_launches")
+
+
+def short(rec):
+    return {k: rec[k] for k in ALSO_KEYS if k in rec}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU implementation, all host threads, bounded sample per step
+# ---------------------------------------------------------------------------------------------------------
+def reference_qp(n, k, sample, steps, warmup, dev):
+    threads = host_cores()
+    prm = synth.solve_params()
+    run_reference_qp(synth.to_numpy(gen_qp_batch(n, k, min(sample, 4096), 7, dev)), prm, threads)  # page-in / thread start
+    # the same stream as the GPU arm's rank 0 (seed 1234, generated on the device when there is one)
+    host = synth.to_numpy(gen_qp_batch(n, k, sample, 1234, dev))
+    times, steps_per, res = [], 0, None
+    for i in range(warmup + steps):
+        res = run_reference_qp(host, prm, threads)
+        if i >= warmup:
+            times.append(res["seconds"])
+            steps_per += res["steps"]
+    total = sum(times)
+    value = steps_per / total
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "steps": steps, "warmup": warmup,
+        "ms_per_step": 1e3 * total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": qp_workload_name(n, k, sample), "n": n, "k": k, "m": 2 * n, "cpu_sample_per_step": sample,
+                   "timing": "std::chrono around the threaded solve loop (unpacking into mini_opt::QP outside)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": res["cores"], "kind": res["kind"],
+                         "sample": f"{sample} QPs n={n} k={k} per step: the first problems of the GPU arm's rank-0 batch, "
+                                   "one QPInteriorPointSolver per std::thread, g++ -O2 -march=x86-64-v3"},
+        "converged_fraction": res["solved"] / sample,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def reference_ik(links, sample):
+    from oracle import oracle_py as O
+    prm = synth.chain_ik_params()
+    ch = synth.chain_ik_batch_numpy(links, sample, seed=4321)
+    threads = host_cores()
+    O.nls_solve_chain("ref", synth.chain_ik_batch_numpy(links, 512, seed=1), prm, nthreads=threads)
+    t0 = time.perf_counter()
+    _, total = O.nls_solve_chain("ref", ch, prm, nthreads=threads)
+    dt = time.perf_counter() - t0
+    return {"impl": "reference", "metric": METRIC, "value": total / dt, "unit": UNIT, "steps": 1, "warmup": 0,
+            "ms_per_step": 1e3 * dt, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"config3: {sample} chain-IK problems, {links} links (CPU sample)"},
+            "nls_problems_per_sec": sample / dt,
+            "cpu_baseline": {"value": total / dt, "unit": UNIT, "cores": threads, "kind": "reference",
+                             "sample": f"{sample} problems, one ConstrainedNonlinearLeastSquares per std::thread"},
+            "e2e": {"value": total / dt, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    dev = None
+    try:
+        import torch
+        if torch.cuda.is_available():
+            dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    except Exception:
+        pass
+    if args.workload == "ik":
+        line = reference_ik(args.links, min(args.batch if args.batch != (1 << 20) else 100000, 20000))
+    else:
+        line = reference_qp(args.n, args.k, args.cpu_sample, args.steps, args.warmup, dev)
+        if args.n == 8 and args.k == 2 and not args.no_also:
+            line["also"] = {"n64": short(reference_qp(64, 16, 8192, 1, 0, dev)), "ik6": short(reference_ik(6, 20000))}
+    line["n_gpus"] = args.gpus
+    print(json.dumps(line), flush=True)
+
+
+SWEEP = {8: (2, [1 << 10, 1 << 14, 1 << 18, 1 << 20, 1 << 24]), 32: (8, [1 << 10, 1 << 14, 1 << 18, 1 << 20]),
+         64: (16, [1 << 10, 1 << 14, 1 << 18, 1 << 20])}
+
+
+def sweep(args, ctx: Ctx):
+    """BASELINE config 5: batch-size sweep x n in {8, 32, 64} at this world size; one JSON line per point. The CPU
+    baseline (N=1) is measured once per n on a capped sample of the largest batch and repeated on every line of that n."""
+    for n, (k, batches) in SWEEP.items():
+        cpu = None
+        for B in batches:
+            if args.sweep_max_batch and B > args.sweep_max_batch:
+                continue
+            steps = 20 if B <= (1 << 18) else (5 if B <= (1 << 20) else 3)
+            sample = {8: 131072, 32: 16384, 64: 4096}[n] if (cpu is None and B >= 16384) else 0
+            rec = qp_pass(ctx, n, k, B, steps, 3, with_e2e=(B <= (1 << 18) and not args.no_e2e),
+                          cpu_sample=0 if args.no_cpu else sample, seed=1234)
+            if rec["cpu_baseline"]:
+                cpu = rec["cpu_baseline"]
+            elif cpu:
+                rec["cpu_baseline"] = cpu
+            rec["sweep"] = True
+            ctx.torch.cuda.empty_cache()
+            if ctx.rank == 0:
+                print(json.dumps(rec), flush=True)
 
 
 def main():
@@ -296,160 +531,37 @@ def main():
     ap.add_argument("--links", type=int, default=6, help="--workload ik: chain links (6-12)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-also", action="store_true", help="skip the config-4 (n=64) and config-3 (IK) records")
+    ap.add_argument("--sweep", action="store_true", help="BASELINE config 5: one JSON line per (n, batch)")
+    ap.add_argument("--sweep-max-batch", type=int, default=0)
     args = ap.parse_args()
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.workload == "ik":
-        ik_main(args, rank, world, local)
-        return
     if args.impl == "reference":
-        reference_arm(args, rank, world)
+        reference_arm(args)
         return
-
-    import torch
-    import torch.distributed as dist
-    from mini_opt_b200 import lib, qp
-
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    L = lib.load()
-    n, k, m, B = args.n, args.k, 2 * args.n, args.batch
-    prm = synth.solve_params()
-    arrs = synth.box_qp_batch_torch(n, k, B, seed=1234 + rank, device=dev)
-    out = qp.alloc_out_torch(B, n, k, m, dev, lagrange=False)
-    stream = torch.cuda.current_stream(dev)
-    fp64_peak = lib.measure_fp64_peak(local)
-
-    def step():
-        qp.solve_batch_device(arrs, prm, out, dev, stream)
-
-    for _ in range(max(args.warmup, 3)):
-        step()
-    torch.cuda.synchronize()
-    launches0 = lib.launch_count()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    with ClockSampler(local) as clocks:
-        t0 = torch.cuda.Event(enable_timing=True)
-        t1 = torch.cuda.Event(enable_timing=True)
-        t0.record(stream)
-        for a, b in evs:
-            a.record(stream)
-            step()
-            b.record(stream)
-        t1.record(stream)
-        torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    launches = lib.launch_count() - launches0
-    total_ms = t0.elapsed_time(t1)
-    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
-    steps_local = int(out.iters.sum().item())
-    solved_local = int((out.status == 0).sum().item())
-    stats = torch.tensor([total_ms, float(steps_local), float(solved_local)], dtype=torch.float64, device=dev)
-    if world > 1:
-        mx = stats.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = stats.clone()
-        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        total_ms, newton_steps, solved = float(mx[0]), float(sm[1]), float(sm[2])
+    ctx = Ctx()
+    ctx.init_gpu()
+    if args.sweep:
+        sweep(args, ctx)
+        ctx.finish()
+        return
+    default_line = args.workload == "qp" and args.n == 8 and args.k == 2 and args.batch == (1 << 20)
+    if args.workload == "ik":
+        B = args.batch if args.batch != (1 << 20) else 100000
+        line = ik_pass(ctx, args.links, B, args.steps, args.warmup, not args.no_e2e, 0 if args.no_cpu else 20000)
     else:
-        newton_steps, solved = float(steps_local), float(solved_local)
-    sec_per_step = total_ms * 1e-3 / args.steps
-    value = newton_steps / sec_per_step
-
-    # roofline of the dominant (only) kernel on this rank
-    F = flops_per_step(n, k, m)
-    tflops = F * steps_local / (kernel_ms * 1e-3) / 1e12
-    alg_bytes = algorithmic_bytes_per_qp(n, k, m) * B
-    peaks = {}
-    try:
-        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
-    except Exception:
-        pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    # ncu dram__bytes_read.sum + dram__bytes_write.sum per pass of the default workload (profiles/r01_tpp_n8_ncu_full_summary.txt:
-    # guess kernel 0.894 + 0.328 GB, iterate kernel 1.247 + 0.364 GB); other shapes: not captured -> null
-    # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from `ncu --set full`, scaled to this launch:
-    # n=8: profiles/r01_tpp_n8_ncu_full_summary.txt; n=64: profiles/r01_wd64_ncu_full_summary.txt (188.7 + 12.4 MB / 6216 QPs,
-    # below the algorithmic bytes because only the lower block triangle of G is fetched; re-reads per Newton step hit L2)
-    traffic = {(8, 2, 1 << 20): 2.833e9, (64, 16, 65536): 201.06e6 / 6216 * 65536}.get((n, k, B))
-    roofline = {
-        "bound": "tensor", "pipe": "fp64: DFMA and DMMA.8x8x4 share one 64 FMA/clk/SM datapath (profiles/r01_dmma_vs_dfma_microbench.txt)",
-        "traffic": traffic, "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak,
-        "kernel": lib.kernel_variant(n, k, m, arrs.flags), "kernel_ms": kernel_ms,
-        "flops_per_newton_step": F, "newton_steps_per_launch": steps_local,
-        "peak_source": "DFMA microbenchmark measured live on this GPU (mo_measure_fp64_peak)",
-        "hbm": {"achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
-                "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
-    }
-
-    # e2e: pinned host buffers through the host entry point (H2D + solve + D2H inside the timed region)
-    e2e = None
-    if not args.no_e2e:
-        host = synth.to_numpy(arrs)
-        keep = []
-        def pin(a):
-            v, p = pinned_copy(L, a)
-            keep.append(p)
-            return v
-        harrs = abi.QPBatchArrays(n=n, k=k, m=m, batch=B, G=pin(host.G), c=pin(host.c), A_eq=pin(host.A_eq) if k else None,
-                                  b_eq=pin(host.b_eq) if k else None, ineq_b=pin(host.ineq_b), flags=host.flags)
-        hout = abi.QPOutArrays(vars=pin(np.zeros((B, n + 2 * m + k))), status=pin(np.zeros(B, dtype=np.int32)),
-                               iters=pin(np.zeros(B, dtype=np.int32)), kkt_final=pin(np.zeros((B, 4))))
-        h2d = sum(a.nbytes for a in (harrs.G, harrs.c, harrs.A_eq, harrs.b_eq, harrs.ineq_b) if a is not None)
-        d2h = hout.vars.nbytes + hout.status.nbytes + hout.iters.nbytes + hout.kkt_final.nbytes
-        for _ in range(2):
-            qp.solve_batch_host(harrs, prm, hout, local)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t_start = time.perf_counter()
-        e2e_steps = max(3, min(args.steps, 5))
-        for _ in range(e2e_steps):
-            qp.solve_batch_host(harrs, prm, hout, local)
-        torch.cuda.synchronize()
-        e2e_sec = (time.perf_counter() - t_start) / e2e_steps
-        ts = torch.tensor([e2e_sec], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
-        assert np.array_equal(hout.iters, out.iters.cpu().numpy()), "host entry point disagrees with device path"
-        e2e = {"value": newton_steps / float(ts[0]), "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
-               "d2h_bytes_per_step": int(d2h) * world, "ms_per_step": 1e3 * float(ts[0]),
-               "qps_per_sec": B * world / float(ts[0])}
-        for p in keep:
-            L.mo_host_free(p)
-
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        threads = host_cores()
-        run_reference_cpu(n, k, 4096, threads)
-        r = run_reference_cpu(n, k, args.cpu_sample, threads)
-        cpu = {"value": r["steps"] / r["seconds"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-               "sample": r["sample"], "qps_per_sec": r["solved"] / r["seconds"], "seconds": r["seconds"]}
-
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * sec_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args), "n": n, "k": k, "m": m, "batch_per_gpu": B,
-                       "l2": "inputs (%.0f MB per pass) exceed the 126 MB L2" % (alg_bytes / 1e6),
-                       "newton_steps_per_qp": newton_steps / (B * world)},
-            "solved_qps_per_sec": solved / sec_per_step, "converged_fraction": solved / (B * world),
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks.summary(),
-        }
+        line = qp_pass(ctx, args.n, args.k, args.batch, args.steps, args.warmup, not args.no_e2e,
+                       0 if args.no_cpu else args.cpu_sample)
+    if default_line and not args.no_also:
+        # BASELINE.json's metric is quoted on n=8 AND n=64; config 3 rides along (same process, same GPU(s))
+        ctx.torch.cuda.empty_cache()
+        n64 = qp_pass(ctx, 64, 16, 65536, max(3, min(args.steps, 10)), 3, not args.no_e2e, 0 if args.no_cpu else 8192)
+        ctx.torch.cuda.empty_cache()
+        ik6 = ik_pass(ctx, 6, 100000, max(2, min(args.steps, 5)), 3, not args.no_e2e, 0 if args.no_cpu else 20000)
+        line["also"] = {"n64": short(n64), "ik6": short(ik6)}
+        line["gpu_launches"] = line["gpu_launches"]  # the main line's own launches; `also` carries its own counts
+    if ctx.rank == 0:
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    ctx.finish()
 
 
 if __name__ == "__main__":

@@ -313,8 +313,15 @@ const char* mo_last_error_string(void);
 /* Measures this GPU's FP64 FMA peak (dependent-free DFMA streams, CUDA events, best of 5) in TFLOP/s: the
  * roofline denominator for the FP64-bound kernels (bench.py). Synchronous. */
 int mo_measure_fp64_peak(int device, double* tflops_out);
+/* Same for the FP64 tensor path (mma.sync.m8n8k4.f64 = SASS DMMA.8x8x4, 8 independent accumulators per warp): the
+ * denominator for the kernels whose O(p^3) work runs on DMMA (n >= 16 factorizations, n >= 32 linearization). */
+int mo_measure_dmma_peak(int device, double* tflops_out);
 
 int mo_abi_version(void);
+
+/* Measurement hook (profiles/, tests): staging mode of the kernels that load per-problem arrays with TMA bulk copies
+ * (cp.async.bulk + mbarrier). 1 = TMA (default), 0 = plain per-lane loads. Returns the previous value. Process-wide. */
+int mo_debug_set_tma(int enabled);
 
 #ifdef __cplusplus
 } /* extern "C" */

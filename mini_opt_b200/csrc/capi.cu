@@ -12,11 +12,14 @@
 #include "wd_launch.h"
 #include "qp_generic.cuh"
 #include "qp_tpp.cuh"
+#include "qp_w16.cuh"
 
 namespace {
 
 thread_local std::string g_last_error;
 std::atomic<long long> g_launches{0};
+// staging mode of the warp16 kernel: 1 = TMA bulk copies (default), 0 = lane loads (A/B measurements, mo_debug_set_tma)
+std::atomic<int> g_w16_tma{1};
 
 int cuda_fail(cudaError_t e, const char* what) {
   g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
@@ -255,6 +258,41 @@ int dispatch_generic(const mo::QPArgs& a, const mo::StepArgs* step, const Device
   }
 }
 
+// warp16 (qp_w16.cuh): every small shape without a thread-per-problem instantiation.
+bool w16_eligible(int n, int k, int m) { return mo::wip_shape_ok(n, k, m); }
+
+template <int PMAX>
+int launch_w16(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
+  const bool box = (a.flags & MO_QP_FLAG_BOX_PAIRS) != 0;
+  const size_t smem = mo::w16_smem_bytes(a.n, a.k, a.m, box);
+  if (smem > (size_t)dev.max_smem_optin) {
+    g_last_error = "problem too large for shared memory: needs " + std::to_string(smem) + " bytes";
+    return MO_ERR_UNSUPPORTED_SHAPE;
+  }
+  auto kernel = mo::qp_warp16_kernel<PMAX>;
+  int bps = 0;
+  MO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32, smem));
+  const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
+  static std::atomic<unsigned> ring{0};
+  unsigned long long* tickets = nullptr;
+  MO_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&tickets), mo::g_w16_tickets));
+  tickets += ring.fetch_add(1) % mo::kW16TicketSlots;
+  MO_CUDA(cudaMemsetAsync(tickets, 0, sizeof(unsigned long long), stream));
+  kernel<<<(int)(a.batch < cap ? a.batch : cap), 32, smem, stream>>>(a, tickets, g_w16_tma.load() ? 1 : 0);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
+int dispatch_w16(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
+  const int p = a.n + a.k;
+  if (p <= 4) return launch_w16<4>(a, dev, stream);
+  if (p <= 8) return launch_w16<8>(a, dev, stream);
+  if (p <= 12) return launch_w16<12>(a, dev, stream);
+  return launch_w16<16>(a, dev, stream);
+}
+
 int dispatch_solve(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
   auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
   const bool vec_ok = aligned16(a.G) && aligned16(a.c) && aligned16(a.A) && aligned16(a.b) && aligned16(a.ib) &&
@@ -276,6 +314,7 @@ int dispatch_solve(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stre
     MO_DM_SHAPES(X)
 #undef X
   }
+  if (w16_eligible(a.n, a.k, a.m)) return dispatch_w16(a, dev, stream);
   return dispatch_generic(a, nullptr, dev, stream);
 }
 
@@ -304,6 +343,8 @@ int64_t mo_qp_vars_stride(int32_t n, int32_t k, int32_t m) { return (int64_t)n +
 
 int mo_abi_version(void) { return MO_ABI_VERSION; }
 
+int mo_debug_set_tma(int enabled) { return g_w16_tma.exchange(enabled ? 1 : 0); }
+
 int64_t mo_kernel_launch_count(void) { return g_launches.load(); }
 
 const char* mo_last_error_string(void) { return g_last_error.c_str(); }
@@ -312,6 +353,7 @@ const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags)
   if (tpp_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY)) return "tpp";
   if (dm_eligible(n, k, m, flags, false, MO_BARRIER_COMPLEMENTARITY))
     return (!dm_use_cta_kernel() && mo::wd_has_shape(n, k)) ? "dmma_warp" : "dmma_cta";
+  if (w16_eligible(n, k, m)) return "warp16";
   switch (generic_threads(n, k)) {
     case 32: return "generic32";
     case 128: return "generic128";

@@ -361,6 +361,206 @@ __device__ __forceinline__ void wd2_column(double* __restrict__ sm, int lane, in
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// LOOK-AHEAD schedule of the block column step (LA = true), the default at n = 64.
+//
+// Measured motivation (profiles/r02_wd64_phase_trace.txt, 7 warps per SM): with the plain left-looking order a column
+// is gather (1.2k cycles) -> diagonal block + forward substitution (2.4k, a pure latency chain: 4 pivot pairs of ~9
+// dependent FP64 operations each, every one of them queueing behind the 16-cycle DMMAs of the other warps of the SM
+// sub-partition) -> panel solve (0.5k), strictly one after the other in the instruction stream of the one warp that
+// owns the problem: 37 % of the kernel is the diagonal chain, during which the warp issues one instruction every ~25 cycles.
+// Here the chain runs UNDER the DMMA work of the same column:
+//   * invariant on entry: diagonal tile (J, J) is completely updated (all panels kk < J applied);
+//   * one basic block holds (a) the register copy + pivot chain of block J and (b) the gather of the off-diagonal
+//     tiles (J+1.., J) over kk < J together with the look-ahead gather of the NEXT diagonal tile (J+1, J+1) over
+//     kk < J -- (b) does not depend on (a), so the scheduler fills the chain's latency slots with DMMA / LDS;
+//   * the gathered tiles stay in their accumulator registers until the panel solve: C-fragment -> A-fragment is four
+//     quad shuffles per tile (wdl_c2a) instead of a store / barrier / load round trip through shared memory;
+//   * after the panel solve of tile (J+1, J) the kk = J update goes straight into the look-ahead accumulator and the
+//     finished diagonal tile (J+1, J+1) is stored: the next column starts with its chain at once;
+//   * the forward substitution of the right-hand side (n = 64) is split: its dot products run in (b), its S_J product
+//     after the panel solve, off the factorization's critical path.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void wdl_c2a(double c0, double c1, int lane, double& a0, double& a1) {
+  // lane 4r + q holds [r][2q], [r][2q+1]; wants [r][q], [r][4 + q]: column q sits in lane 4r + (q >> 1), slot q & 1
+  const int src = (lane & ~3) + ((lane & 3) >> 1);
+  const double t0 = __shfl_sync(0xffffffffu, c0, src), t1 = __shfl_sync(0xffffffffu, c1, src);
+  const double u0 = __shfl_sync(0xffffffffu, c0, src + 2), u1 = __shfl_sync(0xffffffffu, c1, src + 2);
+  a0 = (lane & 1) ? t1 : t0;
+  a1 = (lane & 1) ? u1 : u0;
+}
+
+template <int N, int K, int J>
+__device__ __forceinline__ void wdl_column(double* __restrict__ sm, const int lane, double& chk_io) {
+  using L = WdLayout<N, K>;
+  constexpr int CNT1 = L::NTR - 1 - J;  // off-diagonal tiles of block column J (the rhs tile row included)
+  constexpr bool HASD = J + 1 < L::NT;  // a next diagonal tile exists
+  constexpr int CA = CNT1 > 0 ? CNT1 : 1;
+  constexpr bool FWD = !L::RHS_ROW;     // block forward substitution of the rhs vector
+  double* __restrict__ T = sm;
+  const int r = lane >> 2, q = lane & 3, lr = lane & 7;
+  const int coff = wd_el(r, 2 * q);
+  const int hi = 32 + (lane ^ 8);
+  // ---- (a1) register copy of the finished diagonal block ----
+  double A[8][8];
+  {
+    const double* __restrict__ tile = T + L::tile(J, J);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+      for (int j = 0; j <= i; j += 2) {
+        const double2 v = *reinterpret_cast<const double2*>(tile + wd_el(i, j));
+        A[i][j] = v.x;
+        if (j + 1 <= i) A[i][j + 1] = v.y;
+      }
+    }
+  }
+  // ---- (b) gather: off-diagonal tiles of this column and the next diagonal tile, panels kk < J ----
+  double acc[CA][2], accD[2] = {0.0, 0.0};
+#pragma unroll
+  for (int i = 0; i < CNT1; ++i) {
+    const double2 v = *reinterpret_cast<const double2*>(T + L::tile(J + 1 + i, J) + coff);
+    acc[i][0] = v.x; acc[i][1] = v.y;
+  }
+  if constexpr (HASD) {
+    const double2 v = *reinterpret_cast<const double2*>(T + L::tile(J + 1, J + 1) + coff);
+    accD[0] = v.x; accD[1] = v.y;
+  }
+  double fsa = 0.0, fsb = 0.0, fsc = 0.0, fsd = 0.0;  // forward substitution: sum_kk L(J,kk) D_kk w_kk (row sums over q)
+  if constexpr (J > 0) {
+#pragma unroll
+    for (int kk = 0; kk < J; ++kk) {
+      const double* __restrict__ tb = T + L::tile(J, kk);
+      const double dq0 = sm[L::O_D + 8 * kk + q], dq1 = sm[L::O_D + 8 * kk + 4 + q];
+      const double l0 = tb[lane], l1 = tb[hi];
+      const double b0 = l0 * -dq0, b1 = l1 * -dq1;
+      if constexpr (FWD) {
+        const double z0 = sm[L::O_W + 8 * kk + q] * dq0, z1 = sm[L::O_W + 8 * kk + 4 + q] * dq1;
+        if (kk & 1) { fsc = fma(l0, z0, fsc); fsd = fma(l1, z1, fsd); }
+        else { fsa = fma(l0, z0, fsa); fsb = fma(l1, z1, fsb); }
+      }
+      if constexpr (CNT1 > 0) {
+        double a0[CA], a1[CA];
+#pragma unroll
+        for (int i = 0; i < CNT1; ++i) { a0[i] = tb[64 * (i + 1) + lane]; a1[i] = tb[64 * (i + 1) + hi]; }
+        if constexpr (HASD) {  // tile (J+1, kk) is both operands of the diagonal update
+          const double bd0 = a0[0] * -dq0, bd1 = a1[0] * -dq1;
+          dmma884(accD[0], accD[1], a0[0], bd0);
+#pragma unroll
+          for (int i = 0; i < CNT1; ++i) dmma884(acc[i][0], acc[i][1], a0[i], b0);
+          dmma884(accD[0], accD[1], a1[0], bd1);
+#pragma unroll
+          for (int i = 0; i < CNT1; ++i) dmma884(acc[i][0], acc[i][1], a1[i], b1);
+        } else {
+#pragma unroll
+          for (int i = 0; i < CNT1; ++i) dmma884(acc[i][0], acc[i][1], a0[i], b0);
+#pragma unroll
+          for (int i = 0; i < CNT1; ++i) dmma884(acc[i][0], acc[i][1], a1[i], b1);
+        }
+      }
+    }
+  }
+  // ---- (a2) pivot chain of the 8x8 block, redundantly in every lane (see wd_diag_block) ----
+  double chk = chk_io, dd[8], di[8];
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    const double a00 = A[c][c], a10 = A[c + 1][c], a11 = A[c + 1][c + 1];
+    const double det = fma(a00, a11, -(a10 * a10));
+    const double inv0 = rcp_chain(a00);
+    double xd;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(xd) : "d"(det));
+    const double ed = fma(-det, xd, 1.0), yd = a00 * xd;
+    const double inv1 = fma(yd, fma(ed, ed, ed), yd);  // 1 / d1, d1 = det / a00
+    dd[c] = a00; dd[c + 1] = fma(-(a10 * inv0), a10, a11);
+    di[c] = inv0; di[c + 1] = inv1;
+    chk = fma(inv0, 0.0, chk);
+    chk = fma(inv1, 0.0, chk);
+    A[c + 1][c] = a10 * inv0;
+    double u0[8], u1[8], l0[8];
+#pragma unroll
+    for (int i = c + 2; i < 8; ++i) {
+      u0[i] = A[i][c];
+      l0[i] = u0[i] * inv0;
+      u1[i] = fma(-l0[i], a10, A[i][c + 1]);
+    }
+#pragma unroll
+    for (int i = c + 2; i < 8; ++i) {
+#pragma unroll
+      for (int j = c + 2; j <= i; ++j) A[i][j] = fma(-(u1[i] * u1[j]), inv1, fma(-l0[i], u0[j], A[i][j]));
+      A[i][c] = l0[i];
+      A[i][c + 1] = u1[i] * inv1;
+    }
+  }
+  chk_io = chk;
+  double x[8];  // column lr of inv(L_JJ)
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    double v = i == lr ? 1.0 : 0.0;
+#pragma unroll
+    for (int k = 0; k < i; ++k) v = fma(-A[i][k], x[k], v);
+    x[i] = i >= lr ? v : 0.0;
+  }
+  double myd = dd[0], myinv = di[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) { myd = lr == i ? dd[i] : myd; myinv = lr == i ? di[i] : myinv; }
+  __syncwarp();  // every lane has read the block (and, J > 0, the tiles of the gather)
+  if (lane < 8) {
+    sm[L::O_D + 8 * J + lr] = myd; sm[L::O_INVD + 8 * J + lr] = myinv;
+    double* __restrict__ tile = T + L::tile(J, J);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) tile[wd_el(i, lr)] = x[i];  // S[i][lr]
+  }
+  __syncwarp();
+  // ---- panel solve L(I,J) = C(I,J) S' D^-1 from the accumulators, look-ahead update of the next diagonal tile ----
+  if constexpr (CNT1 > 0) {
+    const double idr = sm[L::O_INVD + 8 * J + r];
+    const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + hi] * idr;
+#pragma unroll
+    for (int i = 0; i < CNT1; ++i) {
+      double a0, a1, p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0;
+      wdl_c2a(acc[i][0], acc[i][1], lane, a0, a1);
+      dmma884(p0, p1, a0, bt0);
+      dmma884(q0, q1, a1, bt1);
+      p0 += q0; p1 += q1;
+      *reinterpret_cast<double2*>(T + L::tile(J + 1 + i, J) + coff) = make_double2(p0, p1);
+      if (HASD && i == 0) {
+        double l0, l1;
+        wdl_c2a(p0, p1, lane, l0, l1);
+        const double bd0 = l0 * -sm[L::O_D + 8 * J + q], bd1 = l1 * -sm[L::O_D + 8 * J + 4 + q];
+        double e0 = 0.0, e1 = 0.0;
+        dmma884(accD[0], accD[1], l0, bd0);
+        dmma884(e0, e1, l1, bd1);
+        *reinterpret_cast<double2*>(T + L::tile(J + 1, J + 1) + coff) = make_double2(accD[0] + e0, accD[1] + e1);
+      }
+    }
+  }
+  // ---- forward substitution, second half: w_J = D_J^-1 S_J (b_J - sum) ----
+  if constexpr (FWD) {
+    double s = (fsa + fsb) + (fsc + fsd);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    const double tr = sm[L::O_R + 8 * J + r] - s;  // t[r] (replicated over q)
+    const int toff = wd_el(q, r);                  // element [q][r]; [4 + q][r] is 16 further
+    const double* __restrict__ S = T + L::tile(J, J);
+    double z0 = S[toff] * tr, z1 = S[toff + 16] * tr;  // S[4h + q][r] t[r]
+    z0 = wd_sum_r(z0); z1 = wd_sum_r(z1);
+    if (r == 0) {
+      sm[L::O_W + 8 * J + q] = z0 * sm[L::O_INVD + 8 * J + q];
+      sm[L::O_W + 8 * J + 4 + q] = z1 * sm[L::O_INVD + 8 * J + 4 + q];
+    }
+  }
+  __syncwarp();
+}
+
+template <int N, int K, int J>
+__device__ __forceinline__ void wdl_columns(double* __restrict__ sm, int lane, double& chk) {
+  if constexpr (J < WdLayout<N, K>::NT) {
+    wdl_column<N, K, J>(sm, lane, chk);
+    wdl_columns<N, K, J + 1>(sm, lane, chk);
+  }
+}
+
 template <int N, int K, int NW, int J>
 __device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, int warp, double& chk) {
   if constexpr (J < WdLayout<N, K>::NT) {
@@ -373,14 +573,16 @@ __device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, in
 // Factor the KKT matrix held in the tiles and solve for the right-hand side held in row 0 of tile row NT.
 // On return sm[O_XV .. O_XV + P) = K^-1 rhs and the cp.async staging of G, A_eq for the next trip is in flight. Returns false on a zero or non-finite pivot (-> MO_QP_FAILED_FACTORIZATION,
 // the batched stand-in for the exception of qp.cc:303-307); with two warps only warp 0 holds the answer.
-template <int N, int K, int NW>
+template <int N, int K, int NW, bool LA>
 __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane, int warp,
                                                 const double* __restrict__ Gp, const double* __restrict__ Ap) {
   using L = WdLayout<N, K>;
   constexpr bool kStageInBacksub = WdLayout<N, K>::STAGE_IN_BACKSUB;
   double chk = 0.0;
   WD_T(1);
-  wd_columns<N, K, NW, 0>(sm, lane, warp, chk);
+  if constexpr (LA) wdl_columns<N, K, 0>(sm, lane, chk);
+  else wd_columns<N, K, NW, 0>(sm, lane, warp, chk);
+  if constexpr (LA) WD_T(3);
   if (NW == 2 && warp != 0) return true;
   // back substitution L' x = w, w = D^-1 L^-1 rhs = row 0 of tile row NT; block J: t = w_J - sum_{I > J} L(I,J)' x_I,
   // x_J = inv(L_JJ)' t with S = inv(L_JJ) stored in the diagonal tile.
@@ -445,8 +647,9 @@ __device__ __forceinline__ void wd_bar() {
   if (NW == 1) __syncwarp(); else __syncthreads();
 }
 
-template <int N, int K, int NW, int MINB>
+template <int N, int K, int NW, int MINB, bool LA>
 __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
+  static_assert(!LA || NW == 1, "the look-ahead schedule is a one-warp schedule");
   using L = WdLayout<N, K>;
   constexpr int P = L::P, M = L::M, NT = L::NT, NTN = L::NTN, VPL = L::VPL, STRIDE = N + 2 * M + K;
   static_assert(NW == 1 || NW == 2, "one or two warps per problem");
@@ -525,7 +728,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
     bool first = true;
     // ---- Solve loop (qp.cc:110-149); each trip = residuals of the current state, bookkeeping, one Newton step ----
     for (;;) {
-      double rhsv[VPL], rhse = 0.0, p0[VPL], p1[VPL], w0[VPL], w1[VPL], i0[VPL], i1[VPL];
+      double rhsv[VPL], rhse = 0.0;
       // publish [x; -y] for the matvec
       if (main_warp) {
 #pragma unroll
@@ -591,7 +794,9 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         if (main_warp) {
         // (2) per-variable residuals, Sigma, r_aug pieces; norms (ComputeErrors, qp.cc:423-437)
         double red[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // |r_d|^2, |r_pe|^2, |r_pi|^2, sum (sz)^2, sum sz, #(s <= 0)
-        double t1[VPL], t2[VPL];
+        // p (r_pi), 1/s and w = z/s are NOT kept across the factorization: step (5) recomputes them from the unchanged
+        // x, s, z, bounds (bit-identical, ~12 FP64 operations per variable) and the factorization gets the registers
+        double t1[VPL], t2[VPL], p0[VPL], p1[VPL], w0[VPL], w1[VPL], i0[VPL], i1[VPL];
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
           const int v = lane + 32 * i;
@@ -686,7 +891,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         __syncwarp();
       }
       if (status >= 0) break;
-      bool ok = wd_factor_solve<N, K, NW>(sm, lane, warp, Gp, Ap);
+      bool ok = wd_factor_solve<N, K, NW, LA>(sm, lane, warp, Gp, Ap);
       if (NW == 2) {
         if (threadIdx.x == 0) *ctl = ok ? 1 : 0;
         __syncthreads();  // also: the back substitution is done, the tiles are free for the next trip's staging
@@ -714,10 +919,13 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         const int v = lane + 32 * i;
         dx[i] = d0[i] = d1[i] = e0[i] = e1[i] = 0.0;
         if (v < N) {
+          const double p0 = (x[i] + b0[i]) - s0[i], p1 = (b1[i] - x[i]) - s1[i];  // as in step (2)
+          const double i0 = fast_rcp(s0[i]), i1 = fast_rcp(s1[i]);
+          const double w0 = z0[i] * i0, w1 = z1[i] * i1;
           dx[i] = XV[v];
-          d0[i] = dx[i] + p0[i]; d1[i] = p1[i] - dx[i];
-          e0[i] = fma(mu, i0[i], -fma(w0[i], d0[i], z0[i]));
-          e1[i] = fma(mu, i1[i], -fma(w1[i], d1[i], z1[i]));
+          d0[i] = dx[i] + p0; d1[i] = p1 - dx[i];
+          e0[i] = fma(mu, i0, -fma(w0, d0[i], z0[i]));
+          e1[i] = fma(mu, i1, -fma(w1, d1[i], z1[i]));
           if (s0[i] + d0[i] <= 0.0 && fabs(d0[i]) > 0) al0 = fmin(al0, -tau * s0[i] / d0[i]);
           if (s1[i] + d1[i] <= 0.0 && fabs(d1[i]) > 0) al0 = fmin(al0, -tau * s1[i] / d1[i]);
           if (z0[i] + e0[i] <= 0.0 && fabs(e0[i]) > 0) al1 = fmin(al1, -tau * z0[i] / e0[i]);

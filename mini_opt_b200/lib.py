@@ -11,13 +11,17 @@ from pathlib import Path
 
 from . import abi
 
+import os
+
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libminiopt_b200.so"
+# MINI_OPT_B200_LIB: harness-only override used by the profiling scripts under tools/ to load an instrumented build
+# (e.g. -DMO_WD_TRACE); the product C/C++ callers link libminiopt_b200.so directly.
+LIB_PATH = Path(os.environ.get("MINI_OPT_B200_LIB", PKG / "libminiopt_b200.so"))
 
 EXPORTS = [
     "mo_qp_params_default", "mo_qp_vars_stride", "mo_qp_ip_solve_batch", "mo_qp_ip_solve_batch_host",
     "mo_qp_ip_newton_step_batch", "mo_qp_kernel_variant", "mo_kernel_launch_count", "mo_last_error_string",
-    "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak",
+    "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak", "mo_measure_dmma_peak", "mo_debug_set_tma",
     "mo_nls_params_default", "mo_nls_linearize_batch", "mo_chain_fk_batch", "mo_nls_solve_chain_ik_batch",
 ]
 
@@ -72,6 +76,10 @@ def load():
     lib.mo_host_free.restype = None
     lib.mo_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
     lib.mo_measure_fp64_peak.restype = C.c_int
+    lib.mo_debug_set_tma.argtypes = [C.c_int]
+    lib.mo_debug_set_tma.restype = C.c_int
+    lib.mo_measure_dmma_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    lib.mo_measure_dmma_peak.restype = C.c_int
     lib.mo_nls_params_default.argtypes = [C.POINTER(abi.MoNlsParams)]
     lib.mo_nls_params_default.restype = None
     lib.mo_nls_linearize_batch.argtypes = [C.POINTER(abi.MoNlsLinearizeArgs), C.c_int, C.c_void_p]
@@ -102,6 +110,13 @@ def kernel_variant(n: int, k: int, m: int, flags: int) -> str:
 
 def launch_count() -> int:
     return int(load().mo_kernel_launch_count())
+
+
+def measure_dmma_peak(device_index: int = 0) -> float:
+    """FP64 tensor-path (DMMA.8x8x4) peak of this GPU in TFLOP/s (live microbenchmark)."""
+    v = C.c_double(0.0)
+    check(load().mo_measure_dmma_peak(int(device_index), C.byref(v)))
+    return float(v.value)
 
 
 def measure_fp64_peak(device_index: int = 0) -> float:

@@ -125,6 +125,17 @@ def chain_ik_batch_numpy(links: int, batch: int, seed: int = 4321, n_eq: int = 0
                              eq_target=np.ascontiguousarray(target[:, 0:1]), ineq_var=var, ineq_a=a, ineq_b=b, x0=x0)
 
 
+def chain_slice(ch: abi.ChainIKArrays, lo: int, hi: int) -> abi.ChainIKArrays:
+    """Problems [lo, hi) of a host chain-IK batch (the per-problem arrays are sliced, the shared ones kept)."""
+    import dataclasses
+    kw = {f.name: getattr(ch, f.name) for f in dataclasses.fields(ch)}
+    for name in ("cost_target", "eq_target", "x0"):
+        if kw[name] is not None:
+            kw[name] = np.ascontiguousarray(kw[name][lo:hi])
+    kw["batch"] = hi - lo
+    return abi.ChainIKArrays(**kw)
+
+
 def chain_ik_params(max_qp_iterations: int = 20) -> abi.NLSParams:
     """Params of TestDualActuatorBalancing (test/nonlinear_test.cc:1086-1102) + the ModPi retraction (:1076-1082).
     ``max_qp_iterations`` defaults to 20 instead of that test's 5: with 5 the REFERENCE itself brings only 9 % of the

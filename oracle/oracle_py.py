@@ -84,6 +84,9 @@ def ref_lib():
         _ref = C.CDLL(str(REF_SO))
         _bind_qp(_ref, "ref", with_threads=True)
         _bind_nls(_ref, "ref", with_threads=True)
+        _ref.ref_qp_solve_batch_timed.restype = C.c_int64
+        _ref.ref_qp_solve_batch_timed.argtypes = [C.POINTER(abi.MoQpBatch), C.POINTER(abi.MoQpParams),
+                                                  C.POINTER(abi.MoQpOut), C.c_int, C.POINTER(C.c_double)]
         _ref.ref_generate_random_qp.restype = C.c_int
         _ref.ref_generate_random_qp.argtypes = [C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 6
         _ref.ref_hardware_concurrency.restype = C.c_int
@@ -117,6 +120,27 @@ def qp_solve(which: str, arrs: abi.QPBatchArrays, params: abi.QPParams, log: boo
     if total < 0:
         raise RuntimeError(f"{which}_qp_solve_batch failed: {total}")
     return out, int(total)
+
+
+def qp_solve_timed(which: str, arrs: abi.QPBatchArrays, params: abi.QPParams, nthreads: int = 1):
+    """Like ``qp_solve`` but returns (outputs, total Newton steps, seconds) where seconds covers the solve loop only:
+    for the reference the problems are unpacked into ``mini_opt::QP`` objects and the outputs allocated before the
+    clock starts (``ref_qp_solve_batch_timed``); the scalar C port is timed around its call."""
+    import time
+    _check_host(arrs)
+    out = abi.alloc_out_numpy(arrs.batch, arrs.n, arrs.k, arrs.m, params.max_iterations, False)
+    b, p, o = arrs.to_c(), params.to_c(), out.to_c()
+    if which == "ref":
+        sec = C.c_double(0.0)
+        total = ref_lib().ref_qp_solve_batch_timed(C.byref(b), C.byref(p), C.byref(o), int(nthreads), C.byref(sec))
+        seconds = float(sec.value)
+    else:
+        t0 = time.perf_counter()
+        total = oracle_lib().oracle_qp_solve_batch(C.byref(b), C.byref(p), C.byref(o))
+        seconds = time.perf_counter() - t0
+    if total < 0:
+        raise RuntimeError(f"{which} timed solve failed: {total}")
+    return out, int(total), seconds
 
 
 def qp_newton_step(which: str, arrs: abi.QPBatchArrays, mu: float, strategy: int, vars_in: np.ndarray):

@@ -219,11 +219,130 @@ static int compute_ldlt(const oq_problem* q, oq_work* w, int include_inequalitie
   return 0;
 }
 
+/* DIAGNOSTIC modes (tools/diagnose_status.py; default 0 = the reference's algorithm). They restate, on the CPU, the two
+ * ways the CUDA kernels solve the Newton system, so that a status difference against the reference can be attributed:
+ *   1  Eigen-pivoted LDLT (as the reference) but ONE substitution solve of the right-hand side, no explicit inverse
+ *      (the generic kernel, qp_generic.cuh)
+ *   2  natural-order unpivoted LDL' + substitution (the tuned kernels: qp_tpp.cuh, qp_wdm.cuh, qp_warp.cuh)
+ *   3  as 2 followed by one step of iterative refinement against the assembled KKT matrix */
+static int g_solve_mode = 0;
+void oracle_set_solve_mode(int mode) { g_solve_mode = mode; }
+
+static int g_diag_n = 0; /* H-block size for the ordering modes */
+static int g_variant = 0; /* diagnostic arithmetic variants: 1 = no FMA, 2 = divide by d instead of multiplying by 1/d,
+                             4 = left-looking (dot-product) accumulation order, 8 = solve divides by d */
+void oracle_set_variant(int v) { g_variant = v; }
+static double vfma(double a, double b, double c) { return (g_variant & 1) ? (a * b + c) : fma(a, b, c); }
+static void unpivoted_ldlt_solve(const double* H, int p, double* x_io, double* scratch) {
+  /* scratch: p*p; lower triangle of H significant. Modes >= 5 factor P K P' with a STATIC permutation chosen from the
+   * assembled diagonal: 5 = H block sorted by descending diagonal (= Eigen's order: its pivot search sees the
+   * not-yet-updated diagonal, LDLT.h:324-326, so equality rows (diagonal 0) come last in natural order);
+   * 6 = variables with diagonal > 1e6 first, natural order otherwise; 7 = natural order, but the LAST TWO pivots are
+   * taken larger-|diagonal|-first dynamically. */
+  double* L = scratch;
+  int perm[256];
+  double xp[256];
+  const int n = g_diag_n;
+  for (int i = 0; i < p; ++i) perm[i] = i;
+  if (g_solve_mode == 5) {
+    for (int i = 1; i < n; ++i) { /* stable insertion sort, descending diagonal */
+      const int v = perm[i];
+      const double key = H[(size_t)v * p + v];
+      int j = i - 1;
+      while (j >= 0 && H[(size_t)perm[j] * p + perm[j]] < key) { perm[j + 1] = perm[j]; --j; }
+      perm[j + 1] = v;
+    }
+  } else if (g_solve_mode == 6) {
+    int cnt = 0, tmp[256];
+    for (int i = 0; i < n; ++i) if (H[(size_t)i * p + i] > 1e6) tmp[cnt++] = i;
+    for (int i = 0; i < n; ++i) if (!(H[(size_t)i * p + i] > 1e6)) tmp[cnt++] = i;
+    for (int i = 0; i < n; ++i) perm[i] = tmp[i];
+  }
+  for (int j = 0; j < p; ++j)
+    for (int i = j; i < p; ++i) {
+      const int a = perm[i], b = perm[j];
+      L[(size_t)j * p + i] = a >= b ? H[(size_t)b * p + a] : H[(size_t)a * p + b];
+    }
+  for (int i = 0; i < p; ++i) xp[i] = x_io[perm[i]];
+  double* x = xp;
+  int swapped = 0;
+  for (int j = 0; j < p; ++j) {
+    double t[256];
+    if (g_solve_mode == 7 && j == p - 2 && fabs(L[(size_t)(p - 1) * p + (p - 1)]) > fabs(L[(size_t)j * p + j])) {
+      /* swap the last two rows/columns */
+      for (int c = 0; c < j; ++c) { double v = L[(size_t)c * p + j]; L[(size_t)c * p + j] = L[(size_t)c * p + p - 1]; L[(size_t)c * p + p - 1] = v; }
+      { double v = L[(size_t)j * p + j]; L[(size_t)j * p + j] = L[(size_t)(p - 1) * p + p - 1]; L[(size_t)(p - 1) * p + p - 1] = v; }
+      { double v = x[j]; x[j] = x[p - 1]; x[p - 1] = v; }
+      swapped = 1;
+    }
+    if (g_variant & 4) { /* left-looking: apply all earlier columns to column j now (Eigen's bordered form, LDLT.h:356-362) */
+      double tmp[256], dot = 0.0;
+      for (int c = 0; c < j; ++c) { tmp[c] = (1.0 / L[(size_t)c * p + c]) * L[(size_t)c * p + j]; }
+      for (int c = 0; c < j; ++c) { tmp[c] = L[(size_t)c * p + j] / L[(size_t)c * p + c]; } /* D_c * L_jc, D stored inverted */
+      for (int c = 0; c < j; ++c) dot = vfma(L[(size_t)c * p + j], tmp[c], dot);
+      L[(size_t)j * p + j] -= dot;
+      for (int i = j + 1; i < p; ++i) {
+        double acc = 0.0;
+        for (int c = 0; c < j; ++c) acc = vfma(L[(size_t)c * p + i], tmp[c], acc);
+        L[(size_t)j * p + i] -= acc;
+      }
+      const double d = L[(size_t)j * p + j];
+      for (int i = j + 1; i < p; ++i) L[(size_t)j * p + i] = (g_variant & 2) ? L[(size_t)j * p + i] / d : L[(size_t)j * p + i] * (1.0 / d);
+      L[(size_t)j * p + j] = 1.0 / d;
+      continue;
+    }
+    const double dj = L[(size_t)j * p + j];
+    const double inv = 1.0 / dj;
+    for (int i = j + 1; i < p; ++i) t[i] = L[(size_t)j * p + i];
+    for (int i = j + 1; i < p; ++i) {
+      const double l = (g_variant & 2) ? t[i] / dj : t[i] * inv;
+      for (int c = j + 1; c <= i; ++c) L[(size_t)c * p + i] = vfma(-l, t[c], L[(size_t)c * p + i]);
+      L[(size_t)j * p + i] = l;
+    }
+    L[(size_t)j * p + j] = inv;
+  }
+  for (int j = 0; j < p; ++j)
+    for (int i = j + 1; i < p; ++i) x[i] = vfma(-L[(size_t)j * p + i], x[j], x[i]);
+  for (int j = 0; j < p; ++j) x[j] = (g_variant & 8) ? x[j] / (1.0 / L[(size_t)j * p + j]) : x[j] * L[(size_t)j * p + j];
+  for (int j = p - 1; j >= 0; --j)
+    for (int i = j + 1; i < p; ++i) x[j] = vfma(-L[(size_t)j * p + i], x[i], x[j]);
+  if (swapped) { double v = x[p - 2]; x[p - 2] = x[p - 1]; x[p - 1] = v; }
+  for (int i = 0; i < p; ++i) x_io[perm[i]] = x[i];
+}
+
 /* The four block mat-vecs against H^-1 shared by SolveForUpdate (qp.cc:350-356) and
  * SolveForUpdateNoInequalities (qp.cc:379-385). */
 static void apply_inverse(const oq_problem* q, oq_work* w, const double* r_x, const double* r_pe) {
   const int n = q->n, k = q->k, p = w->p;
   double *dx = XB(w->delta, q), *dy = YB(w->delta, q);
+  if (g_solve_mode != 0) { /* [dx; -dy] = K^-1 [-r_x; -r_pe] by substitution */
+    double u[256], rhs[256];
+    for (int i = 0; i < n; ++i) u[i] = -r_x[i];
+    for (int i = 0; i < k; ++i) u[n + i] = -r_pe[i];
+    memcpy(rhs, u, sizeof(double) * p);
+    g_diag_n = n;
+    if (g_solve_mode == 1) {
+      eigen_ldlt_solve_inplace(w->LD, w->transp, p, u, 1);
+    } else {
+      unpivoted_ldlt_solve(w->H, p, u, w->Hinv);
+      if (g_solve_mode == 3) {
+        double res[256];
+        for (int i = 0; i < p; ++i) {
+          double acc = rhs[i];
+          for (int j = 0; j < p; ++j) {
+            const double h = i >= j ? w->H[(size_t)j * p + i] : w->H[(size_t)i * p + j];
+            acc = fma(-h, u[j], acc);
+          }
+          res[i] = acc;
+        }
+        unpivoted_ldlt_solve(w->H, p, res, w->Hinv);
+        for (int i = 0; i < p; ++i) u[i] += res[i];
+      }
+    }
+    for (int i = 0; i < n; ++i) dx[i] = u[i];
+    for (int i = 0; i < k; ++i) dy[i] = -u[n + i];
+    return;
+  }
   for (int i = 0; i < n; ++i) {
     double acc = 0.0;
     for (int j = 0; j < n; ++j) acc += w->Hinv[(size_t)j * p + i] * -r_x[j];

@@ -7,6 +7,7 @@
 // sources where they lie under /root/reference by oracle/Makefile into oracle/_ref/libminiopt_ref.so.
 // Nothing from the reference is copied into this repository.
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <limits>
@@ -89,15 +90,18 @@ void LoadVars(const mo_qp_batch& b, int count, const double* src, Eigen::VectorX
   for (int i = 0; i < count; ++i) (*v)[n + count + k + i] = src[n + m + k + i];
 }
 
+// `prepared`: problems [0, batch) already unpacked (the timed entry point keeps UnpackQP outside its clock,
+// BASELINE.md section 4); nullptr: unpack on the fly.
 void SolveRange(const mo_qp_batch& b, const mo_qp_params& params, const mo_qp_out& out, int64_t begin,
-                int64_t end, std::atomic<int64_t>* total_iters) {
+                int64_t end, std::atomic<int64_t>* total_iters, const std::vector<QP>* prepared = nullptr) {
   const auto ref_params = ToParams(params);
   const int64_t stride = b.n + 2 * b.m + b.k;
-  QP qp;
+  QP local;
   QPInteriorPointSolver solver;  // re-used across problems like test/qp_test.cc:531-539
   int64_t iters_sum = 0;
   for (int64_t p = begin; p < end; ++p) {
-    UnpackQP(b, p, &qp);
+    if (!prepared) UnpackQP(b, p, &local);
+    const QP& qp = prepared ? (*prepared)[p] : local;
     const int count = static_cast<int>(qp.constraints.size());
     int status = -1;
     std::size_t iters = 0;
@@ -174,9 +178,31 @@ int64_t ref_qp_solve_batch(const mo_qp_batch* b, const mo_qp_params* params, con
   for (int t = 0; t < nthreads; ++t) {
     const int64_t lo = t * chunk, hi = std::min<int64_t>(b->batch, lo + chunk);
     if (lo >= hi) break;
-    pool.emplace_back(SolveRange, std::cref(*b), std::cref(*params), std::cref(*out), lo, hi, &total);
+    pool.emplace_back(SolveRange, std::cref(*b), std::cref(*params), std::cref(*out), lo, hi, &total, nullptr);
   }
   for (auto& th : pool) th.join();
+  return total.load();
+}
+
+// Same, for timing: every problem is unpacked into a mini_opt::QP first (outside the clock), then the threaded solve
+// loop alone is timed with std::chrono; *seconds_out receives the wall time of that loop.
+int64_t ref_qp_solve_batch_timed(const mo_qp_batch* b, const mo_qp_params* params, const mo_qp_out* out,
+                                 int nthreads, double* seconds_out) {
+  if (!b || !params || !out || !out->vars || !out->status || !out->iters || !seconds_out) return MO_ERR_INVALID_ARGUMENT;
+  if (nthreads < 1) nthreads = 1;
+  std::vector<QP> prepared(static_cast<std::size_t>(b->batch));
+  for (int64_t p = 0; p < b->batch; ++p) UnpackQP(*b, p, &prepared[p]);
+  std::atomic<int64_t> total{0};
+  std::vector<std::thread> pool;
+  const int64_t chunk = (b->batch + nthreads - 1) / nthreads;
+  const auto t0 = std::chrono::steady_clock::now();
+  for (int t = 0; t < nthreads; ++t) {
+    const int64_t lo = t * chunk, hi = std::min<int64_t>(b->batch, lo + chunk);
+    if (lo >= hi) break;
+    pool.emplace_back(SolveRange, std::cref(*b), std::cref(*params), std::cref(*out), lo, hi, &total, &prepared);
+  }
+  for (auto& th : pool) th.join();
+  *seconds_out = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return total.load();
 }
 

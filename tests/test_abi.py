@@ -70,7 +70,9 @@ def test_argument_validation_precedes_cuda():
         qp.solve_batch_host(arrs, abi.QPParams(), out, 0)
     assert e.value.code == abi.MO_ERR_INVALID_ARGUMENT
     assert lib.kernel_variant(8, 2, 16, abi.MO_QP_FLAG_BOX_PAIRS) == "tpp"
-    assert lib.kernel_variant(7, 2, 14, abi.MO_QP_FLAG_BOX_PAIRS).startswith("generic")
+    assert lib.kernel_variant(7, 2, 14, abi.MO_QP_FLAG_BOX_PAIRS) == "warp16"  # every n + k <= 16, m <= 32 shape
+    assert lib.kernel_variant(12, 3, 24, 0) == "warp16"
+    assert lib.kernel_variant(20, 4, 40, abi.MO_QP_FLAG_BOX_PAIRS).startswith("generic")
 
 
 def test_no_cpu_fallback_without_device():
