@@ -39,6 +39,7 @@ sys.path.insert(0, str(ROOT / "tools"))
 
 from mini_opt_b200 import abi, synth  # noqa: E402
 
+E2E_FORMAT = "compact"  # --e2e-format
 METRIC = "ip_newton_steps_per_sec"
 UNIT = "steps/s"
 
@@ -270,12 +271,23 @@ def qp_pass(ctx: Ctx, n, k, B, steps, warmup, with_e2e=True, cpu_sample=0, seed=
             v, p = pinned_copy(L, a)
             keep.append(p)
             return v
-        harrs = abi.QPBatchArrays(n=n, k=k, m=m, batch=B, G=pin(host.G), c=pin(host.c), A_eq=pin(host.A_eq) if k else None,
-                                  b_eq=pin(host.b_eq) if k else None, ineq_b=pin(host.ineq_b), flags=host.flags)
-        hout = abi.QPOutArrays(vars=pin(np.zeros((B, n + 2 * m + k))), status=pin(np.zeros(B, dtype=np.int32)),
-                               iters=pin(np.zeros(B, dtype=np.int32)), kkt_final=pin(np.zeros((B, 4))))
+        if E2E_FORMAT == "compact":
+            # what a host caller holding Eigen objects hands over: the lower triangle of G (all the reference reads,
+            # qp.cc:289,404), one box for the batch, and x_block() + status + iteration count + KKT norms back
+            assert (host.ineq_b == host.ineq_b[0]).all()
+            harrs = abi.QPBatchArrays(n=n, k=k, m=m, batch=B, G=pin(qp.pack_lower(host.G)), c=pin(host.c),
+                                      A_eq=pin(host.A_eq) if k else None, b_eq=pin(host.b_eq) if k else None,
+                                      ineq_b=pin(np.ascontiguousarray(host.ineq_b[0])),
+                                      flags=host.flags | abi.MO_QP_FLAG_PACKED_G | abi.MO_QP_FLAG_UNIFORM_BOX)
+            hout = abi.QPOutArrays(vars=None, status=pin(np.zeros(B, dtype=np.int32)), iters=pin(np.zeros(B, dtype=np.int32)),
+                                   kkt_final=pin(np.zeros((B, 4))), x=pin(np.zeros((B, n))))
+        else:
+            harrs = abi.QPBatchArrays(n=n, k=k, m=m, batch=B, G=pin(host.G), c=pin(host.c), A_eq=pin(host.A_eq) if k else None,
+                                      b_eq=pin(host.b_eq) if k else None, ineq_b=pin(host.ineq_b), flags=host.flags)
+            hout = abi.QPOutArrays(vars=pin(np.zeros((B, n + 2 * m + k))), status=pin(np.zeros(B, dtype=np.int32)),
+                                   iters=pin(np.zeros(B, dtype=np.int32)), kkt_final=pin(np.zeros((B, 4))))
         h2d = sum(a.nbytes for a in (harrs.G, harrs.c, harrs.A_eq, harrs.b_eq, harrs.ineq_b) if a is not None)
-        d2h = hout.vars.nbytes + hout.status.nbytes + hout.iters.nbytes + hout.kkt_final.nbytes
+        d2h = sum(a.nbytes for a in (hout.vars, hout.x, hout.status, hout.iters, hout.kkt_final) if a is not None)
         for _ in range(2):
             qp.solve_batch_host(harrs, prm, hout, ctx.local)
         ctx.barrier()
@@ -287,7 +299,11 @@ def qp_pass(ctx: Ctx, n, k, B, steps, warmup, with_e2e=True, cpu_sample=0, seed=
         torch.cuda.synchronize()
         e2e_sec = ctx.reduce([(time.perf_counter() - t_start) / e2e_steps], "max")[0]
         assert np.array_equal(hout.iters, out.iters.cpu().numpy()), "host entry point disagrees with device path"
-        e2e = {"value": newton_steps / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * ctx.world,
+        if hout.x is not None:
+            assert np.array_equal(hout.x, out.vars[:, :n].cpu().numpy()), "host entry point x disagrees with device path"
+        e2e = {"format": ("packed lower-triangle G + one box for the batch in; x, status, iters, kkt_final out"
+                          if E2E_FORMAT == "compact" else "full G, per-problem bounds in; [x|s|y|z], status, iters, kkt_final out"),
+               "value": newton_steps / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * ctx.world,
                "d2h_bytes_per_step": int(d2h) * ctx.world, "ms_per_step": 1e3 * e2e_sec,
                "qps_per_sec": B * ctx.world / e2e_sec}
         for p in keep:
@@ -534,7 +550,11 @@ def main():
     ap.add_argument("--no-also", action="store_true", help="skip the config-4 (n=64) and config-3 (IK) records")
     ap.add_argument("--sweep", action="store_true", help="BASELINE config 5: one JSON line per (n, batch)")
     ap.add_argument("--sweep-max-batch", type=int, default=0)
+    ap.add_argument("--e2e-format", default="compact", choices=["compact", "full"],
+                    help="host buffers of the e2e leg: compact = packed lower-triangle G, one box per batch, x-only output")
     args = ap.parse_args()
+    global E2E_FORMAT
+    E2E_FORMAT = args.e2e_format
     if args.impl == "reference":
         reference_arm(args)
         return

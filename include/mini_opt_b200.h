@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MO_ABI_VERSION 1
+#define MO_ABI_VERSION 2
 
 /* ---- return codes of the entry points (not per-problem status) ---- */
 typedef enum mo_error {
@@ -55,7 +55,14 @@ enum {
   /* Caller promises m == 2n and constraint 2i is (i,+1,b), constraint 2i+1 is (i,-1,b), i.e.
    * Var(i) >= lo_i, Var(i) <= hi_i with ineq_b = {-lo_0, hi_0, -lo_1, hi_1, ...}. ineq_var / ineq_a
    * are then not read (may be NULL). This is the box layout of BASELINE configs 2-5. */
-  MO_QP_FLAG_BOX_PAIRS = 1
+  MO_QP_FLAG_BOX_PAIRS = 1,
+  /* HOST entry points only (mo_qp_ip_solve_batch_host / _host_multi): compact input formats that cut the bytes
+   * crossing PCIe; they are expanded on the device into the layout above before the solve.
+   * PACKED_G: G is [batch][n(n+1)/2], the lower triangle column by column (column j holds rows j..n-1) -- exactly the
+   * entries the reference reads (qp.cc:289, :404); 288 instead of 512 bytes per problem at n = 8.
+   * UNIFORM_BOX (needs BOX_PAIRS): ineq_b is ONE [2n] vector {-lo_0, hi_0, ...} shared by the whole batch. */
+  MO_QP_FLAG_PACKED_G = 2,
+  MO_QP_FLAG_UNIFORM_BOX = 4
 };
 
 /*
@@ -102,12 +109,15 @@ typedef struct mo_qp_params {
  *  [11]    alpha_probe.primal [12] alpha_probe.dual [13] mu_affine   (NaN unless PREDICTOR_CORRECTOR) */
 
 typedef struct mo_qp_out {
-  double* vars;      /* [batch][n+2m+k] = [x | s | y | z] (qp.cc:548-582). In/out for MO_GUESS_USER_PROVIDED. */
+  double* vars;      /* [batch][n+2m+k] = [x | s | y | z] (qp.cc:548-582). In/out for MO_GUESS_USER_PROVIDED.
+                        HOST entry points: may be NULL when `x` is given (only x_block() is copied back). */
   int32_t* status;   /* [batch] MO_QP_*                                                  */
   int32_t* iters;    /* [batch] == outputs.iterations.size()                             */
   double* kkt_final; /* optional [batch][4]: kkt_final of the last iteration              */
   double* lagrange;  /* optional [batch][2]: {min y, ||y||_inf} (qp.cc:539-546); NaN if k == 0 */
   double* iter_log;  /* optional [batch][max_iterations][MO_QP_ITER_LOG_STRIDE]           */
+  double* x;         /* optional [batch][n]: x_block() alone (qp.hpp:187). HOST entry points only: with vars == NULL
+                        the device-to-host traffic per problem drops from 8(n+2m+k) to 8n bytes.     */
 } mo_qp_out;
 
 /* Fills *p with the reference defaults (qp.hpp:136-163). */
@@ -131,6 +141,15 @@ int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params
  */
 int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
                               int device);
+
+/*
+ * Same as mo_qp_ip_solve_batch_host over SEVERAL devices of one node from one process: the batch is split into
+ * n_devices contiguous shards, one host thread and its own stream ring per device, no collective, every shard's results
+ * written straight into the caller's single output arrays ("gathered only at the end": the gather is the D2H copies).
+ * `devices[i]` are CUDA device ordinals. Returns the first error of any shard.
+ */
+int mo_qp_ip_solve_batch_host_multi(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
+                                    const int* devices, int n_devices);
 
 /* Pinned (page-locked) host memory: buffers allocated here are DMA'd directly by the *_host entry points;
  * pageable buffers work too but are staged by the driver. */

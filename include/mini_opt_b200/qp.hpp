@@ -171,7 +171,7 @@ class QPInteriorPointSolver {
     prm.decrease_mu_only_on_small_error = params.decrease_mu_only_on_small_error;
     prm.initial_guess_method = static_cast<int>(params.initial_guess_method);
     prm.initialize_mu_with_complementarity = params.initialize_mu_with_complementarity;
-    mo_qp_out out{vars.data(), status.data(), iters.data(), kkt.data(), lag.data(), nullptr};
+    mo_qp_out out{vars.data(), status.data(), iters.data(), kkt.data(), lag.data(), nullptr, nullptr};
     const int rc = mo_qp_ip_solve_batch_host(&batch, &prm, &out, device);
     if (rc == MO_ERR_INVALID_PARAMS) throw std::invalid_argument("invalid QPInteriorPointSolver::Params (qp.cc:76-82)");
     if (rc == MO_ERR_INVALID_ARGUMENT) throw std::invalid_argument("invalid problem");

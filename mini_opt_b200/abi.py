@@ -11,7 +11,7 @@ from dataclasses import dataclass
 
 import numpy as np
 
-MO_ABI_VERSION = 1
+MO_ABI_VERSION = 2
 
 # mo_error
 MO_OK = 0
@@ -38,6 +38,8 @@ MO_GUESS_SOLVE_EQUALITY_CONSTRAINED = 1
 MO_GUESS_USER_PROVIDED = 2
 
 MO_QP_FLAG_BOX_PAIRS = 1
+MO_QP_FLAG_PACKED_G = 2
+MO_QP_FLAG_UNIFORM_BOX = 4
 MO_QP_ITER_LOG_STRIDE = 14
 
 _dp = C.c_void_p  # data pointers are passed as raw addresses (host or device)
@@ -84,6 +86,7 @@ class MoQpOut(C.Structure):
         ("kkt_final", _dp),
         ("lagrange", _dp),
         ("iter_log", _dp),
+        ("x", _dp),
     ]
 
 
@@ -168,10 +171,11 @@ class QPOutArrays:
     kkt_final: object = None
     lagrange: object = None
     iter_log: object = None
+    x: object = None
 
     def to_c(self) -> MoQpOut:
         return MoQpOut(_addr(self.vars), _addr(self.status), _addr(self.iters), _addr(self.kkt_final),
-                       _addr(self.lagrange), _addr(self.iter_log))
+                       _addr(self.lagrange), _addr(self.iter_log), _addr(self.x))
 
 
 def alloc_out_numpy(batch: int, n: int, k: int, m: int, max_iterations: int = 0, log: bool = False) -> QPOutArrays:

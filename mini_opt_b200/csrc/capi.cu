@@ -6,6 +6,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "qp_dmma.cuh"
@@ -97,8 +98,11 @@ int check_batch(const mo_qp_batch* b) {
       return MO_ERR_INVALID_ARGUMENT;
     }
   }
+  if ((b->flags & MO_QP_FLAG_UNIFORM_BOX) && !(b->flags & MO_QP_FLAG_BOX_PAIRS)) return MO_ERR_INVALID_ARGUMENT;
   return MO_OK;
 }
+
+constexpr int kHostOnlyFlags = MO_QP_FLAG_PACKED_G | MO_QP_FLAG_UNIFORM_BOX;
 
 mo::QPArgs make_args(const mo_qp_batch* b, const mo_qp_params* p, const mo_qp_out* o) {
   mo::QPArgs a{};
@@ -370,6 +374,10 @@ int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params
   if (rc) return rc;
   if (problems->batch == 0) return MO_OK;
   if (!out->vars || !out->status || !out->iters) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->flags & kHostOnlyFlags) {
+    g_last_error = "MO_QP_FLAG_PACKED_G / MO_QP_FLAG_UNIFORM_BOX are input formats of the *_host entry points";
+    return MO_ERR_INVALID_ARGUMENT;
+  }
   DeviceInfo dev;
   rc = device_info(device, &dev);
   if (rc) return rc;
@@ -414,14 +422,14 @@ struct Slot {
 };
 struct HostCtx {
   Slot slots[3];
+  std::mutex mu;  // one host pipeline per device at a time; different devices run concurrently (_host_multi)
 };
 HostCtx g_host[64];
-std::mutex g_host_mu;
 
 inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
 struct ChunkLayout {
-  size_t G, c, A, b, ivar, ia, ib, icount, vars, status, iters, kkt, lag, log, total;
+  size_t G, c, A, b, ivar, ia, ib, icount, vars, status, iters, kkt, lag, log, Gpacked, xonly, total;
 };
 
 ChunkLayout chunk_layout(const mo_qp_batch& B, const mo_qp_params& P, const mo_qp_out& O, long long C) {
@@ -443,8 +451,159 @@ ChunkLayout chunk_layout(const mo_qp_batch& B, const mo_qp_params& P, const mo_q
   L.kkt = take(O.kkt_final ? C * 4 * d : 0);
   L.lag = take(O.lagrange ? C * 2 * d : 0);
   L.log = take(O.iter_log ? C * (size_t)P.max_iterations * MO_QP_ITER_LOG_STRIDE * d : 0);
+  L.Gpacked = take((B.flags & MO_QP_FLAG_PACKED_G) ? C * (n * (n + 1) / 2) * d : 0);
+  L.xonly = take(O.x ? C * n * d : 0);
   L.total = off;
   return L;
+}
+
+// Device-side expansion of the compact host formats (MO_QP_FLAG_PACKED_G / MO_QP_FLAG_UNIFORM_BOX) into the layout the
+// solve kernels read, and compaction of x_block() for the x-only output: HBM-speed passes that replace PCIe bytes.
+__global__ void __launch_bounds__(256) unpack_g_kernel(const double* __restrict__ packed, double* __restrict__ G, int n,
+                                                       long long count) {
+  const long long per = (long long)n * (n + 1) / 2, total = count * per;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const long long p = idx / per;
+    int e = (int)(idx - p * per), j = 0;
+    while (e >= n - j) { e -= n - j; ++j; }  // column j holds rows j..n-1
+    G[p * n * n + (long long)j * n + (j + e)] = packed[idx];
+  }
+}
+__global__ void __launch_bounds__(256) broadcast_box_kernel(const double* __restrict__ box, double* __restrict__ ib, int m,
+                                                            long long count) {
+  const long long total = count * m;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x)
+    ib[idx] = box[idx % m];
+}
+__global__ void __launch_bounds__(256) gather_x_kernel(const double* __restrict__ vars, double* __restrict__ x, int n,
+                                                       long long stride, long long count) {
+  const long long total = count * n;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const long long p = idx / n;
+    x[idx] = vars[p * stride + (idx - p * n)];
+  }
+}
+inline int grid_for(long long total, int sms) {
+  const long long want = (total + 255) / 256, cap = (long long)sms * 8;
+  return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+int solve_host_range(const mo_qp_batch& B, const mo_qp_params& P, const mo_qp_out& O, long long begin, long long end,
+                     int device) {
+  DeviceInfo dev;
+  int rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  HostCtx& ctx = g_host[device];
+  std::lock_guard<std::mutex> lk(ctx.mu);
+
+  const size_t n = B.n, k = B.k, m = B.m, d = sizeof(double), vs = n + 2 * m + k;
+  const bool packed = (B.flags & MO_QP_FLAG_PACKED_G) != 0, ubox = (B.flags & MO_QP_FLAG_UNIFORM_BOX) != 0;
+  const size_t gpack = n * (n + 1) / 2;
+  const size_t per_problem = (n * n + n + k * n + k + 2 * m + vs + 8) * d +
+                             (O.iter_log ? (size_t)P.max_iterations * MO_QP_ITER_LOG_STRIDE * d : 0);
+  const long long total = end - begin;
+  long long C = (long long)((size_t(96) << 20) / per_problem);
+  if (C < 4096) C = 4096;
+  if (C > total) C = total;
+  const ChunkLayout L = chunk_layout(B, P, O, C);
+  for (Slot& s : ctx.slots) {
+    if (!s.stream) MO_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    if (s.cap < L.total) {
+      if (s.dbuf) MO_CUDA(cudaFree(s.dbuf));
+      s.dbuf = nullptr; s.cap = 0;
+      MO_CUDA(cudaMalloc(&s.dbuf, L.total));
+      s.cap = L.total;
+    }
+  }
+  const bool user_guess = P.initial_guess_method == MO_GUESS_USER_PROVIDED;
+  int slot_i = 0;
+  for (long long lo = begin; lo < end; lo += C, slot_i = (slot_i + 1) % 3) {
+    const long long cnt = (end - lo < C) ? end - lo : C;
+    Slot& s = ctx.slots[slot_i];
+    MO_CUDA(cudaStreamSynchronize(s.stream));  // previous use of this slot has drained
+    char* D = s.dbuf;
+    auto h2d = [&](size_t off, const void* src, size_t stride_bytes) -> cudaError_t {
+      if (!src || !stride_bytes) return cudaSuccess;
+      return cudaMemcpyAsync(D + off, (const char*)src + lo * stride_bytes, cnt * stride_bytes,
+                             cudaMemcpyHostToDevice, s.stream);
+    };
+    if (packed) {
+      MO_CUDA(h2d(L.Gpacked, B.G, gpack * d));
+      unpack_g_kernel<<<grid_for(cnt * (long long)gpack, dev.sms), 256, 0, s.stream>>>(
+          (const double*)(D + L.Gpacked), (double*)(D + L.G), (int)n, cnt);
+      g_launches.fetch_add(1);
+    } else {
+      MO_CUDA(h2d(L.G, B.G, n * n * d));
+    }
+    MO_CUDA(h2d(L.c, B.c, n * d));
+    MO_CUDA(h2d(L.A, B.A_eq, k * n * d));
+    MO_CUDA(h2d(L.b, B.b_eq, k * d));
+    MO_CUDA(h2d(L.ivar, B.ineq_var, m * sizeof(int32_t)));
+    MO_CUDA(h2d(L.ia, B.ineq_a, m * d));
+    if (ubox) {  // one [2n] vector for the batch: staged in the (still unused) vars area, broadcast on the device
+      MO_CUDA(cudaMemcpyAsync(D + L.vars, B.ineq_b, m * d, cudaMemcpyHostToDevice, s.stream));
+      broadcast_box_kernel<<<grid_for(cnt * (long long)m, dev.sms), 256, 0, s.stream>>>(
+          (const double*)(D + L.vars), (double*)(D + L.ib), (int)m, cnt);
+      g_launches.fetch_add(1);
+    } else {
+      MO_CUDA(h2d(L.ib, B.ineq_b, m * d));
+    }
+    MO_CUDA(h2d(L.icount, B.ineq_count, sizeof(int32_t)));
+    if (user_guess) MO_CUDA(h2d(L.vars, O.vars, vs * d));
+    mo_qp_batch db = B;
+    db.flags = B.flags & ~kHostOnlyFlags;
+    db.batch = cnt;
+    db.G = (const double*)(D + L.G); db.c = (const double*)(D + L.c);
+    db.A_eq = k ? (const double*)(D + L.A) : nullptr; db.b_eq = k ? (const double*)(D + L.b) : nullptr;
+    db.ineq_var = B.ineq_var ? (const int32_t*)(D + L.ivar) : nullptr;
+    db.ineq_a = B.ineq_a ? (const double*)(D + L.ia) : nullptr;
+    db.ineq_b = m ? (const double*)(D + L.ib) : nullptr;
+    db.ineq_count = B.ineq_count ? (const int32_t*)(D + L.icount) : nullptr;
+    mo_qp_out dout{};
+    dout.vars = (double*)(D + L.vars); dout.status = (int32_t*)(D + L.status); dout.iters = (int32_t*)(D + L.iters);
+    dout.kkt_final = O.kkt_final ? (double*)(D + L.kkt) : nullptr;
+    dout.lagrange = O.lagrange ? (double*)(D + L.lag) : nullptr;
+    dout.iter_log = O.iter_log ? (double*)(D + L.log) : nullptr;
+    if (dout.iter_log)
+      MO_CUDA(cudaMemsetAsync(dout.iter_log, 0xff, cnt * (size_t)P.max_iterations * MO_QP_ITER_LOG_STRIDE * d, s.stream));
+    const mo::QPArgs a = make_args(&db, &P, &dout);
+    rc = dispatch_solve(a, dev, s.stream);
+    if (rc) return rc;
+    auto d2h = [&](void* dst, size_t off, size_t stride_bytes) -> cudaError_t {
+      if (!dst || !stride_bytes) return cudaSuccess;
+      return cudaMemcpyAsync((char*)dst + lo * stride_bytes, D + off, cnt * stride_bytes, cudaMemcpyDeviceToHost,
+                             s.stream);
+    };
+    if (O.x) {
+      gather_x_kernel<<<grid_for(cnt * (long long)n, dev.sms), 256, 0, s.stream>>>(
+          (const double*)(D + L.vars), (double*)(D + L.xonly), (int)n, (long long)vs, cnt);
+      g_launches.fetch_add(1);
+      MO_CUDA(d2h(O.x, L.xonly, n * d));
+    }
+    MO_CUDA(d2h(O.vars, L.vars, vs * d));
+    MO_CUDA(d2h(O.status, L.status, sizeof(int32_t)));
+    MO_CUDA(d2h(O.iters, L.iters, sizeof(int32_t)));
+    MO_CUDA(d2h(O.kkt_final, L.kkt, 4 * d));
+    MO_CUDA(d2h(O.lagrange, L.lag, 2 * d));
+    MO_CUDA(d2h(O.iter_log, L.log, (size_t)P.max_iterations * MO_QP_ITER_LOG_STRIDE * d));
+    MO_CUDA(cudaGetLastError());
+  }
+  for (Slot& s : ctx.slots) MO_CUDA(cudaStreamSynchronize(s.stream));
+  return MO_OK;
+}
+
+int check_host_call(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out) {
+  if (!problems || !params || !out) return MO_ERR_INVALID_ARGUMENT;
+  int rc = check_batch(problems);
+  if (rc) return rc;
+  rc = check_params(params);
+  if (rc) return rc;
+  if (problems->batch == 0) return MO_OK;
+  if ((!out->vars && !out->x) || !out->status || !out->iters) return MO_ERR_INVALID_ARGUMENT;
+  if (params->initial_guess_method == MO_GUESS_USER_PROVIDED && !out->vars) return MO_ERR_INVALID_ARGUMENT;
+  return MO_OK;
 }
 
 }  // namespace
@@ -453,7 +612,7 @@ extern "C" {
 
 void* mo_host_alloc(size_t bytes) {
   void* p = nullptr;
-  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
     g_last_error = std::string("cudaHostAlloc: ") + cudaGetErrorString(cudaGetLastError());
     return nullptr;
   }
@@ -466,90 +625,33 @@ void mo_host_free(void* p) {
 
 int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
                               int device) {
-  if (!problems || !params || !out) return MO_ERR_INVALID_ARGUMENT;
-  int rc = check_batch(problems);
-  if (rc) return rc;
-  rc = check_params(params);
-  if (rc) return rc;
-  const mo_qp_batch& B = *problems;
-  if (B.batch == 0) return MO_OK;
-  if (!out->vars || !out->status || !out->iters) return MO_ERR_INVALID_ARGUMENT;
-  DeviceInfo dev;
-  rc = device_info(device, &dev);
-  if (rc) return rc;
-  DeviceGuard guard(device);
-  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
-  std::lock_guard<std::mutex> lk(g_host_mu);
-  HostCtx& ctx = g_host[device];
+  const int rc = check_host_call(problems, params, out);
+  if (rc || problems->batch == 0) return rc;
+  return solve_host_range(*problems, *params, *out, 0, problems->batch, device);
+}
 
-  const size_t n = B.n, k = B.k, m = B.m, d = sizeof(double), vs = n + 2 * m + k;
-  const size_t per_problem = (n * n + n + k * n + k + 2 * m + vs + 8) * d +
-                             (out->iter_log ? (size_t)params->max_iterations * MO_QP_ITER_LOG_STRIDE * d : 0);
-  long long C = (long long)((size_t(96) << 20) / per_problem);
-  if (C < 4096) C = 4096;
-  if (C > B.batch) C = B.batch;
-  const ChunkLayout L = chunk_layout(B, *params, *out, C);
-  for (Slot& s : ctx.slots) {
-    if (!s.stream) MO_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-    if (s.cap < L.total) {
-      if (s.dbuf) MO_CUDA(cudaFree(s.dbuf));
-      s.dbuf = nullptr; s.cap = 0;
-      MO_CUDA(cudaMalloc(&s.dbuf, L.total));
-      s.cap = L.total;
-    }
+int mo_qp_ip_solve_batch_host_multi(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
+                                    const int* devices, int n_devices) {
+  if (!devices || n_devices < 1 || n_devices > 64) return MO_ERR_INVALID_ARGUMENT;
+  const int rc = check_host_call(problems, params, out);
+  if (rc || problems->batch == 0) return rc;
+  if (n_devices == 1) return solve_host_range(*problems, *params, *out, 0, problems->batch, devices[0]);
+  // contiguous shards, one host thread (and one 3-stream ring) per device, no exchange between them
+  const long long B = problems->batch, shard = (B + n_devices - 1) / n_devices;
+  std::vector<int> rcs(n_devices, MO_OK);
+  std::vector<std::string> errs(n_devices);
+  std::vector<std::thread> pool;
+  for (int i = 0; i < n_devices; ++i) {
+    const long long lo = i * shard, hi = lo + shard < B ? lo + shard : B;
+    if (lo >= hi) break;
+    pool.emplace_back([&, i, lo, hi]() {
+      rcs[i] = solve_host_range(*problems, *params, *out, lo, hi, devices[i]);
+      if (rcs[i]) errs[i] = g_last_error;  // g_last_error is thread local
+    });
   }
-  const bool user_guess = params->initial_guess_method == MO_GUESS_USER_PROVIDED;
-  int slot_i = 0;
-  for (long long lo = 0; lo < B.batch; lo += C, slot_i = (slot_i + 1) % 3) {
-    const long long cnt = (B.batch - lo < C) ? B.batch - lo : C;
-    Slot& s = ctx.slots[slot_i];
-    MO_CUDA(cudaStreamSynchronize(s.stream));  // previous use of this slot has drained
-    char* D = s.dbuf;
-    auto h2d = [&](size_t off, const void* src, size_t stride_bytes) -> cudaError_t {
-      if (!src || !stride_bytes) return cudaSuccess;
-      return cudaMemcpyAsync(D + off, (const char*)src + lo * stride_bytes, cnt * stride_bytes,
-                             cudaMemcpyHostToDevice, s.stream);
-    };
-    MO_CUDA(h2d(L.G, B.G, n * n * d));
-    MO_CUDA(h2d(L.c, B.c, n * d));
-    MO_CUDA(h2d(L.A, B.A_eq, k * n * d));
-    MO_CUDA(h2d(L.b, B.b_eq, k * d));
-    MO_CUDA(h2d(L.ivar, B.ineq_var, m * sizeof(int32_t)));
-    MO_CUDA(h2d(L.ia, B.ineq_a, m * d));
-    MO_CUDA(h2d(L.ib, B.ineq_b, m * d));
-    MO_CUDA(h2d(L.icount, B.ineq_count, sizeof(int32_t)));
-    if (user_guess) MO_CUDA(h2d(L.vars, out->vars, vs * d));
-    mo_qp_batch db = B;
-    db.batch = cnt;
-    db.G = (const double*)(D + L.G); db.c = (const double*)(D + L.c);
-    db.A_eq = k ? (const double*)(D + L.A) : nullptr; db.b_eq = k ? (const double*)(D + L.b) : nullptr;
-    db.ineq_var = B.ineq_var ? (const int32_t*)(D + L.ivar) : nullptr;
-    db.ineq_a = B.ineq_a ? (const double*)(D + L.ia) : nullptr;
-    db.ineq_b = m ? (const double*)(D + L.ib) : nullptr;
-    db.ineq_count = B.ineq_count ? (const int32_t*)(D + L.icount) : nullptr;
-    mo_qp_out dout{};
-    dout.vars = (double*)(D + L.vars); dout.status = (int32_t*)(D + L.status); dout.iters = (int32_t*)(D + L.iters);
-    dout.kkt_final = out->kkt_final ? (double*)(D + L.kkt) : nullptr;
-    dout.lagrange = out->lagrange ? (double*)(D + L.lag) : nullptr;
-    dout.iter_log = out->iter_log ? (double*)(D + L.log) : nullptr;
-    if (dout.iter_log)
-      MO_CUDA(cudaMemsetAsync(dout.iter_log, 0xff, cnt * (size_t)params->max_iterations * MO_QP_ITER_LOG_STRIDE * d, s.stream));
-    const mo::QPArgs a = make_args(&db, params, &dout);
-    rc = dispatch_solve(a, dev, s.stream);
-    if (rc) return rc;
-    auto d2h = [&](void* dst, size_t off, size_t stride_bytes) -> cudaError_t {
-      if (!dst || !stride_bytes) return cudaSuccess;
-      return cudaMemcpyAsync((char*)dst + lo * stride_bytes, D + off, cnt * stride_bytes, cudaMemcpyDeviceToHost,
-                             s.stream);
-    };
-    MO_CUDA(d2h(out->vars, L.vars, vs * d));
-    MO_CUDA(d2h(out->status, L.status, sizeof(int32_t)));
-    MO_CUDA(d2h(out->iters, L.iters, sizeof(int32_t)));
-    MO_CUDA(d2h(out->kkt_final, L.kkt, 4 * d));
-    MO_CUDA(d2h(out->lagrange, L.lag, 2 * d));
-    MO_CUDA(d2h(out->iter_log, L.log, (size_t)params->max_iterations * MO_QP_ITER_LOG_STRIDE * d));
-  }
-  for (Slot& s : ctx.slots) MO_CUDA(cudaStreamSynchronize(s.stream));
+  for (std::thread& t : pool) t.join();
+  for (int i = 0; i < n_devices; ++i)
+    if (rcs[i]) { g_last_error = errs[i]; return rcs[i]; }
   return MO_OK;
 }
 

@@ -71,6 +71,22 @@ def solve_batch_host(arrs: abi.QPBatchArrays, params: abi.QPParams, out: abi.QPO
     lib.check(L.mo_qp_ip_solve_batch_host(C.byref(b), C.byref(p), C.byref(o), int(device_index)))
 
 
+def solve_batch_host_multi(arrs: abi.QPBatchArrays, params: abi.QPParams, out: abi.QPOutArrays, devices):
+    """``mo_qp_ip_solve_batch_host_multi``: one host batch sharded over several devices of this node from one process."""
+    L = lib.load()
+    b, p, o = arrs.to_c(), params.to_c(), out.to_c()
+    devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+    lib.check(L.mo_qp_ip_solve_batch_host_multi(C.byref(b), C.byref(p), C.byref(o), devs, len(devices)))
+
+
+def pack_lower(G: np.ndarray) -> np.ndarray:
+    """[B, n, n] column-major problems -> [B, n(n+1)/2] packed lower triangles (MO_QP_FLAG_PACKED_G: column j holds rows
+    j..n-1). ``G[p][c][r]`` is element (r, c)."""
+    B, n, _ = G.shape
+    cols = [G[:, j, j:] for j in range(n)]
+    return np.ascontiguousarray(np.concatenate(cols, axis=1))
+
+
 def newton_step_device(arrs: abi.QPBatchArrays, mu: float, strategy: int, vars_t, device, want=("delta", "ip", "kkt")):
     """``mo_qp_ip_newton_step_batch`` on device tensors; ``vars_t`` [B, n+2m+k] is updated in place."""
     import torch

@@ -404,3 +404,48 @@ def test_dmma_kernels_log_and_user_guess_vs_oracle(dev, oracle, n, k, dmma_varia
     ref, _ = oracle.qp_solve("oracle", arrs, prm, user_vars=uv)
     out = gpu_solve(arrs, prm, dev, user_vars=uv)
     compare(out, ref, n, min_same=0.99, min_x=0.99)
+
+
+def test_host_entry_compact_formats(dev, oracle):
+    """mo_qp_ip_solve_batch_host with MO_QP_FLAG_PACKED_G | MO_QP_FLAG_UNIFORM_BOX in and x-only out gives exactly the
+    device path's results (the formats are expanded on the device before the same kernels run)."""
+    from mini_opt_b200 import qp
+    for n, k, B in ((8, 2, 20000), (32, 8, 3000), (12, 3, 3000)):
+        arrs = synth.box_qp_batch_numpy(n, k, B, seed=321 + n, explicit_constraints=False)
+        prm = synth.solve_params()
+        want = gpu_solve(arrs, prm, dev)
+        compact = abi.QPBatchArrays(n=n, k=k, m=2 * n, batch=B, G=qp.pack_lower(arrs.G), c=arrs.c, A_eq=arrs.A_eq,
+                                    b_eq=arrs.b_eq, ineq_b=np.ascontiguousarray(arrs.ineq_b[0]),
+                                    flags=arrs.flags | abi.MO_QP_FLAG_PACKED_G | abi.MO_QP_FLAG_UNIFORM_BOX)
+        out = abi.QPOutArrays(vars=None, status=np.zeros(B, dtype=np.int32), iters=np.zeros(B, dtype=np.int32),
+                              kkt_final=np.zeros((B, 4)), x=np.zeros((B, n)))
+        qp.solve_batch_host(compact, prm, out, 0)
+        assert np.array_equal(out.status, want.status) and np.array_equal(out.iters, want.iters)
+        assert np.array_equal(out.x, want.vars[:, :n])
+        np.testing.assert_array_equal(out.kkt_final, want.kkt_final)
+    # the device entry point refuses the host-only formats
+    import torch
+    d = qp.to_device(compact, dev)
+    o = qp.alloc_out_torch(B, n, k, 2 * n, dev)
+    from mini_opt_b200 import lib
+    with pytest.raises(lib.MiniOptError) as e:
+        qp.solve_batch_device(d, prm, o, dev)
+    assert e.value.code == abi.MO_ERR_INVALID_ARGUMENT
+
+
+def test_host_entry_multi_device(dev):
+    """mo_qp_ip_solve_batch_host_multi: the batch sharded over the visible devices from one process equals the
+    single-device result (no collective; each shard lands in its slice of the caller's arrays)."""
+    import torch
+    from mini_opt_b200 import qp
+    ndev = torch.cuda.device_count()
+    devices = list(range(min(ndev, 4))) if ndev > 1 else [0, 0]  # one GPU: two shards queue on the same device
+    B, n, k = 30001, 8, 2
+    arrs = synth.box_qp_batch_numpy(n, k, B, seed=909, explicit_constraints=False)
+    prm = synth.solve_params()
+    one = abi.alloc_out_numpy(B, n, k, 2 * n)
+    qp.solve_batch_host(arrs, prm, one, 0)
+    many = abi.alloc_out_numpy(B, n, k, 2 * n)
+    qp.solve_batch_host_multi(arrs, prm, many, devices)
+    assert np.array_equal(one.status, many.status) and np.array_equal(one.iters, many.iters)
+    np.testing.assert_array_equal(one.vars, many.vars)
