@@ -573,7 +573,7 @@ __device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, in
 // Factor the KKT matrix held in the tiles and solve for the right-hand side held in row 0 of tile row NT.
 // On return sm[O_XV .. O_XV + P) = K^-1 rhs and the cp.async staging of G, A_eq for the next trip is in flight. Returns false on a zero or non-finite pivot (-> MO_QP_FAILED_FACTORIZATION,
 // the batched stand-in for the exception of qp.cc:303-307); with two warps only warp 0 holds the answer.
-template <int N, int K, int NW, bool LA>
+template <int N, int K, int NW, bool LA, bool PBS>
 __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane, int warp,
                                                 const double* __restrict__ Gp, const double* __restrict__ Ap) {
   using L = WdLayout<N, K>;
@@ -589,13 +589,63 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
   const double* __restrict__ T = sm;
   double* __restrict__ XS = sm + L::O_XV;
   const int r = lane >> 2, q = lane & 3;
+  const int toff = wd_el(q, r);  // element [q][r]; [4 + q][r] is 16 further
+  if constexpr (PBS) {
+    // Software-pipelined and fully unrolled: the only term of block J on the dependent chain is the one of the block
+    // just solved, x_{J+1}, which arrives REPLICATED in registers (wd_sum_r leaves x_J[q], x_J[4 + q] in every lane with
+    // that q -- the operand layout of the next product, so no store / barrier / load sits on the chain); the terms of
+    // the older blocks (I >= J + 2) were summed one block earlier, under the shuffles of that block's chain.
+    double xr0 = 0.0, xr1 = 0.0, pa = 0.0, pb = 0.0;
+#pragma unroll
+    for (int JJ = 0; JJ < L::NT; ++JJ) {
+      const int J = L::NT - 1 - JJ;
+      const double* __restrict__ tj = T + 64 * (J * L::NTR - (J * (J - 1)) / 2);  // tile (J, J); tile (I, J) = tj + 64 (I - J)
+      double sa = pa, sb = pb;
+      if (J + 1 < L::NT) { sa = fma(tj[64 + toff], xr0, sa); sb = fma(tj[64 + toff + 16], xr1, sb); }
+      double sq = sa + sb;
+      sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+      sq += __shfl_xor_sync(0xffffffffu, sq, 2);
+      const double wr = L::RHS_ROW ? tj[64 * (L::NT - J) + wd_el(0, r)] : sm[L::O_W + 8 * J + r];
+      const double tr = wr - sq;  // t[r] (replicated over q)
+      double x0 = tj[lane] * tr, x1 = tj[32 + (lane ^ 8)] * tr;  // S[r][4h + q] t[r]
+      x0 = wd_sum_r(x0); x1 = wd_sum_r(x1);
+      // partial sums of block J - 1 over I >= J + 1 (x_I in shared memory since the previous trip's barrier)
+      double na = 0.0, nb = 0.0, nc = 0.0, nd = 0.0;
+      if (J > 0) {
+        const double* __restrict__ tp = T + 64 * ((J - 1) * L::NTR - ((J - 1) * (J - 2)) / 2);  // tile (J-1, J-1)
+#pragma unroll
+        for (int I = J + 1; I < L::NT; I += 2) {
+          const double* __restrict__ ti = tp + 64 * (I - J + 1);
+          na = fma(ti[toff], XS[8 * I + q], na);
+          nb = fma(ti[toff + 16], XS[8 * I + 4 + q], nb);
+          if (I + 1 < L::NT) {
+            nc = fma(ti[64 + toff], XS[8 * I + 8 + q], nc);
+            nd = fma(ti[64 + toff + 16], XS[8 * I + 12 + q], nd);
+          }
+        }
+      }
+      pa = na + nc; pb = nb + nd;
+      xr0 = x0; xr1 = x1;
+      if (r == 0) { XS[8 * J + q] = x0; XS[8 * J + 4 + q] = x1; }
+      __syncwarp();
+      if (kStageInBacksub && J < L::NTN) {  // block column J of L is consumed: stage the next trip's G, A into it
+        double* __restrict__ dst = sm + 64 * (J * L::NTR - (J * (J - 1)) / 2) + lane;
+        const int hi = 32 + (lane ^ 8) - lane;
+        const double* __restrict__ g = Gp + (q + 8 * J) * N + r + 8 * J;
+#pragma unroll
+        for (int I = J; I < L::NTN; ++I, dst += 64, g += 8) { cp_async8(dst, g); cp_async8(dst + hi, g + 4 * N); }
+        const double* __restrict__ ap = Ap + (q + 8 * J) * K + r;
+#pragma unroll
+        for (int I = L::NTN; I < L::NT; ++I, dst += 64, ap += 8) { cp_async8(dst, ap); cp_async8(dst + hi, ap + 4 * K); }
+      }
+    }
+  } else {
 #pragma unroll 1
   for (int J = L::NT - 1; J >= 0; --J) {
     const double* __restrict__ tj = T + 64 * (J * L::NTR - (J * (J - 1)) / 2);  // tile (J, J); tile (I, J) = tj + 64 (I - J)
     // t[r] = w[r] - sum_I sum_k L(I,J)[k][r] x_I[k]: the tiles are read TRANSPOSED (element [4h + q][r], two contiguous
     // 128-byte runs per request in this layout), so the sum over k is two accumulators per lane plus a reduction over
     // q (2 shuffle levels), and t lands where the second product needs it (lane group r) without a broadcast.
-    const int toff = wd_el(q, r);  // element [q][r]; [4 + q][r] is 16 further
     double sa = 0.0, sb = 0.0, sc = 0.0, sd = 0.0;
     for (int I = J + 1; I < L::NT; I += 2) {
       const double* __restrict__ ti = tj + 64 * (I - J);
@@ -631,6 +681,7 @@ __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lan
       }
     }
   }
+  }
   if (kStageInBacksub) cp_async_commit();
   WD_T(5);
   return chk == chk;
@@ -647,7 +698,7 @@ __device__ __forceinline__ void wd_bar() {
   if (NW == 1) __syncwarp(); else __syncthreads();
 }
 
-template <int N, int K, int NW, int MINB, bool LA>
+template <int N, int K, int NW, int MINB, bool LA, bool PBS>
 __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
   static_assert(!LA || NW == 1, "the look-ahead schedule is a one-warp schedule");
   using L = WdLayout<N, K>;
@@ -679,23 +730,31 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
 #pragma unroll
       for (int J = 0; J < NT; ++J) { T[L::tile(NT, J) + lane] = 0.0; T[L::tile(NT, J) + 32 + (lane ^ 8)] = 0.0; }
     }
-    double x[VPL], s0[VPL], s1[VPL], z0[VPL], z1[VPL], b0[VPL], b1[VPL], cv[VPL];
+    double x[VPL], s0[VPL], s1[VPL], z0[VPL], z1[VPL];
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      const int v = lane + 32 * i;
-      x[i] = 0.0; s0[i] = s1[i] = z0[i] = z1[i] = 1.0; b0[i] = b1[i] = 1.0; cv[i] = 0.0;
-      if (v < N && main_warp) {
-        cv[i] = a.c[prob * N + v];
-        const double2 bb = *reinterpret_cast<const double2*>(a.ib + prob * M + 2 * v);
-        b0[i] = bb.x; b1[i] = bb.y;
+    for (int i = 0; i < VPL; ++i) { x[i] = 0.0; s0[i] = s1[i] = z0[i] = z1[i] = 1.0; }
+    // c, b_eq and the box bounds are NOT held in registers for the life of the problem: the three places that need
+    // them re-read their 40 bytes per lane (L1 / L2 hits), and the factorization in between gets the registers
+    const double* __restrict__ cp = a.c + prob * N;
+    const double* __restrict__ ibp = a.ib + prob * M;
+    auto load_bounds = [&](double (&b0)[VPL], double (&b1)[VPL]) {
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        const int v = lane + 32 * i;
+        b0[i] = b1[i] = 1.0;
+        if (v < N && main_warp) {
+          const double2 bb = __ldg(reinterpret_cast<const double2*>(ibp + 2 * v));
+          b0[i] = bb.x; b1[i] = bb.y;
+        }
       }
-    }
+    };
     double y = 0.0;
-    const double be = (isy && main_warp) ? a.b[prob * K + lane] : 0.0;
     int status = -1, iters = 0;
     // ComputeInitialGuess tail for my variables (qp.cc:462-481): clamp in list order (ClampX, qp.hpp:43-53),
     // s = max(1e-9, a x + b), z = 1/s.
     auto clamp_init = [&]() {
+      double b0[VPL], b1[VPL];
+      load_bounds(b0, b1);
 #pragma unroll
       for (int i = 0; i < VPL; ++i) {
         double xv = x[i];
@@ -744,9 +803,10 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
 #pragma unroll
           for (int I = J; I < NT; ++I) { T[L::tile(I, J) + lane] = 0.0; T[L::tile(I, J) + 32 + (lane ^ 8)] = 0.0; }
       }
+      const double be = (isy && main_warp) ? __ldg(a.b + prob * K + lane) : 0.0;
       if (guess_pending) {  // KKT system without Sigma, rhs = -[c; b_eq]
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) rhsv[i] = -cv[i];
+        for (int i = 0; i < VPL; ++i) rhsv[i] = (lane + 32 * i < N && main_warp) ? -__ldg(cp + lane + 32 * i) : 0.0;
         rhse = -be;
       } else {
         // (1) EvaluateKKTConditions (qp.cc:391-420): symmetric matvec [[G, A'],[A, 0]] [x; -y] over the stored tiles;
@@ -796,13 +856,14 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         double red[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // |r_d|^2, |r_pe|^2, |r_pi|^2, sum (sz)^2, sum sz, #(s <= 0)
         // p (r_pi), 1/s and w = z/s are NOT kept across the factorization: step (5) recomputes them from the unchanged
         // x, s, z, bounds (bit-identical, ~12 FP64 operations per variable) and the factorization gets the registers
-        double t1[VPL], t2[VPL], p0[VPL], p1[VPL], w0[VPL], w1[VPL], i0[VPL], i1[VPL];
+        double t1[VPL], t2[VPL], p0[VPL], p1[VPL], w0[VPL], w1[VPL], i0[VPL], i1[VPL], b0[VPL], b1[VPL];
+        load_bounds(b0, b1);
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
           const int v = lane + 32 * i;
           t1[i] = t2[i] = p0[i] = p1[i] = w0[i] = w1[i] = i0[i] = i1[i] = 0.0;
           if (v < N) {
-            const double base = (NW == 1 ? R[v] : R[v] + RC[v]) + cv[i];
+            const double base = (NW == 1 ? R[v] : R[v] + RC[v]) + __ldg(cp + v);
             p0[i] = (x[i] + b0[i]) - s0[i]; p1[i] = (b1[i] - x[i]) - s1[i];
             i0[i] = fast_rcp(s0[i]); i1[i] = fast_rcp(s1[i]);
             w0[i] = z0[i] * i0[i]; w1[i] = z1[i] * i1[i];
@@ -891,7 +952,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         __syncwarp();
       }
       if (status >= 0) break;
-      bool ok = wd_factor_solve<N, K, NW, LA>(sm, lane, warp, Gp, Ap);
+      bool ok = wd_factor_solve<N, K, NW, LA, PBS>(sm, lane, warp, Gp, Ap);
       if (NW == 2) {
         if (threadIdx.x == 0) *ctl = ok ? 1 : 0;
         __syncthreads();  // also: the back substitution is done, the tiles are free for the next trip's staging
@@ -913,7 +974,8 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
       }
       if (main_warp) {
       // (5) ds, dz (qp.cc:359-363), step lengths (:485-507), state update (:196-199)
-      double al0 = 1.0, al1 = 1.0, dx[VPL], d0[VPL], d1[VPL], e0[VPL], e1[VPL];
+      double al0 = 1.0, al1 = 1.0, dx[VPL], d0[VPL], d1[VPL], e0[VPL], e1[VPL], b0[VPL], b1[VPL];
+      load_bounds(b0, b1);
 #pragma unroll
       for (int i = 0; i < VPL; ++i) {
         const int v = lane + 32 * i;

@@ -11,13 +11,16 @@ namespace mo {
 // Measured on B200 (ms per batch): n=64 64K QPs: 6 CTAs/SM (smem limit) 18.9; n=32 256K: 12 CTAs/SM (168 registers, no
 // spills) 18.5, 16 (128 registers) 19.6, 20 (96) 23.4; n=16 512K: 12 -> 19.3, 16 -> 19.1, 24 -> 23.5.
 #ifndef MO_WD_LA64
-#define MO_WD_LA64 true
+#define MO_WD_LA64 false
 #endif
 #ifndef MO_WD_LA32
 #define MO_WD_LA32 false
 #endif
 #ifndef MO_WD_LA16
 #define MO_WD_LA16 false
+#endif
+#ifndef MO_WD_PBS
+#define MO_WD_PBS true
 #endif
 #define MO_WD_SHAPES(X) X(64, 16, 1, 7, MO_WD_LA64) X(32, 8, 1, 12, MO_WD_LA32) X(16, 8, 1, 16, MO_WD_LA16)
 #ifdef MO_WD_AB_BUILD
@@ -29,7 +32,7 @@ namespace mo {
 template <int N, int K, int NW, int MINB, bool LA>
 static cudaError_t launch_wd(const QPArgs& a, int sms, cudaStream_t stream) {
   using L = WdLayout<N, K>;
-  auto kernel = qp_wd_kernel<N, K, NW, MINB, LA>;
+  auto kernel = qp_wd_kernel<N, K, NW, MINB, LA, (NW == 1) && MO_WD_PBS>;
   static thread_local int configured_dev = -1;
   static thread_local int bps = 0;
   int cur = 0;

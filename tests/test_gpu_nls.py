@@ -17,6 +17,13 @@ from make_golden import IK_SETS, LINEARIZE_SHAPES  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 
+# (identical termination + all three counts, identical termination) floors per golden set = measured on B200 minus 0.3 %
+# and 4 sigma of the sample (profiles/r02_gpu_test_fractions.jsonl). With an equality row the REFERENCE itself ends 40 % of
+# these synthetic problems in QP failure and its C restatement matches its counts on 70 %: chaos of the problem family,
+# which is why every problem additionally goes through assert_quality.
+IK_FLOORS = {"ik6": (0.93, 0.93), "ik12": (0.93, 0.93), "ik6q5": (0.93, 0.93), "ik8eq": (0.65, 0.65)}
+IK_ORACLE_FLOOR = {6: 0.93, 9: 0.93, 12: 0.93}
+
 
 @pytest.fixture(scope="module")
 def dev():
@@ -44,6 +51,34 @@ def gpu_nls(ch, prm, dev):
 
 def counts_same(a, b_term, b_it, b_qp, b_ls):
     return (a.termination == b_term) & (a.iterations == b_it) & (a.qp_iterations == b_qp) & (a.ls_steps == b_ls)
+
+
+def _record(**kw):
+    """MO_RECORD_FRACTIONS=<file>: append the measured fractions (the thresholds below are pinned to measured - 0.3 %)."""
+    import json, os
+    path = os.environ.get("MO_RECORD_FRACTIONS")
+    if path:
+        kw["test"] = os.environ.get("PYTEST_CURRENT_TEST", "")
+        with open(path, "a") as f:
+            f.write(json.dumps(kw) + "\n")
+
+
+def assert_quality(out, ch, ref_errors, ref_termination, tag):
+    """Trajectory-independent properties for EVERY problem, including those whose iteration counts differ from the
+    reference's (rounding-chaotic trajectories are allowed to differ, they are not allowed to be worse):
+    the returned x is finite and inside the joint limits, the final Errors{f, equality} are not worse than the
+    reference's (x 1.001 + 1e-9) on all but a measured sliver, and the termination histogram matches."""
+    assert np.isfinite(out.x).all()
+    var, a, b = np.asarray(ch.ineq_var), np.asarray(ch.ineq_a), np.asarray(ch.ineq_b)
+    viol = a[None, :] * out.x[:, var] + b[None, :]
+    assert viol.min() >= -1e-9, viol.min()  # a x + b >= 0 for every constraint of every problem
+    merit_gpu = out.errors[:, 0] + out.errors[:, 1]
+    merit_ref = ref_errors[:, 0] + ref_errors[:, 1]
+    not_worse = np.mean(merit_gpu <= merit_ref * 1.001 + 1e-9)
+    hist = lambda t: np.bincount(np.asarray(t, dtype=np.int64), minlength=8) / len(t)
+    hdiff = float(np.abs(hist(out.termination) - hist(ref_termination)).max())
+    _record(kind="quality", tag=tag, not_worse=float(not_worse), hist_diff=hdiff)
+    return not_worse, hdiff
 
 
 @pytest.mark.parametrize("seed", range(6))
@@ -87,11 +122,17 @@ def test_chain_ik_golden(dev, golden_nls, tag, links, neq, qpi, B):
     out = gpu_nls(ch, synth.chain_ik_params(qpi), dev)
     g = golden_nls
     same = counts_same(out, g[f"{tag}_termination"], g[f"{tag}_iterations"], g[f"{tag}_qp_iterations"], g[f"{tag}_ls_steps"])
-    need = 0.65 if neq else 0.93
-    assert same.mean() >= need, same.mean()
-    assert (out.termination == g[f"{tag}_termination"]).mean() >= need
+    term = (out.termination == g[f"{tag}_termination"]).mean()
     dx = np.abs(out.x - g[f"{tag}_x"]).max(axis=1)
-    assert np.mean(dx[same] < 1e-6) >= 0.9, np.mean(dx[same] < 1e-6)
+    _record(kind="ik_golden", tag=tag, problems=B, same=float(same.mean()), termination=float(term),
+            x6=float(np.mean(dx[same] < 1e-6)), x9=float(np.mean(dx[same] < 1e-9)))
+    need_same, need_term = IK_FLOORS[tag]
+    assert same.mean() >= need_same, same.mean()
+    assert term >= need_term, term
+    assert np.mean(dx[same] < 1e-6) >= 0.97, np.mean(dx[same] < 1e-6)
+    not_worse, hdiff = assert_quality(out, ch, g[f"{tag}_errors"], g[f"{tag}_termination"], tag)
+    assert not_worse >= 0.99, not_worse
+    assert hdiff <= 0.01, hdiff
 
 
 @pytest.mark.parametrize("links,strategy", [(6, abi.MO_LS_ARMIJO_BACKTRACK), (9, abi.MO_LS_POLYNOMIAL_APPROXIMATION),
@@ -103,9 +144,13 @@ def test_chain_ik_vs_oracle(dev, oracle, links, strategy):
     ref, _ = oracle.nls_solve_chain("oracle", ch, prm)
     out = gpu_nls(ch, prm, dev)
     same = counts_same(out, ref.termination, ref.iterations, ref.qp_iterations, ref.ls_steps)
-    assert same.mean() >= 0.93, same.mean()
     dx = np.abs(out.x - ref.x).max(axis=1)
-    assert np.mean(dx[same] < 1e-6) >= 0.9
+    _record(kind="ik_oracle", links=links, strategy=int(strategy), problems=1500, same=float(same.mean()),
+            termination=float((out.termination == ref.termination).mean()), x6=float(np.mean(dx[same] < 1e-6)))
+    assert same.mean() >= IK_ORACLE_FLOOR[links], same.mean()
+    assert np.mean(dx[same] < 1e-6) >= 0.97
+    not_worse, hdiff = assert_quality(out, ch, ref.errors, ref.termination, f"oracle{links}")
+    assert not_worse >= 0.99 and hdiff <= 0.01, (not_worse, hdiff)
     ok = same & (ref.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL)
     np.testing.assert_allclose(out.errors[ok], ref.errors[ok], atol=1e-9)
 
