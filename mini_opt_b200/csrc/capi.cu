@@ -661,6 +661,7 @@ int mo_qp_ip_solve_batch_host_multi(const mo_qp_batch* problems, const mo_qp_par
 // nonlinear least squares entry points
 // ---------------------------------------------------------------------------------------------
 #include "nls_chain.cuh"
+#include "nls_linearize_dmma.cuh"
 
 namespace {
 
@@ -750,8 +751,30 @@ int mo_nls_linearize_batch(const mo_nls_linearize_args* g, int device, void* cud
   mo::LinearizeArgs a{g->n, g->r_cost, g->cost_block, g->r_eq, g->m, g->batch, g->x, g->J_cost, g->r_cost_v, g->J_eq,
                       g->r_eq_v, g->lambda, g->ineq_var, g->ineq_a, g->ineq_b, g->G, g->c, g->A_eq, g->b_eq,
                       g->ineq_b_shifted, g->errors};
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  // n = 32 .. 64 (multiple of 8), even row count, 16-byte aligned J / r: the DMMA kernel (nls_linearize_dmma.cuh)
+  auto aligned16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15u) == 0; };
+  if (g->n % 8 == 0 && g->n >= 32 && g->n <= 64 && g->r_cost >= 8 && g->r_cost % 2 == 0 && aligned16(g->J_cost) &&
+      aligned16(g->r_cost_v)) {
+    auto launch = [&](auto kernel) -> int {
+      int bps = 0;
+      MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32, 0));
+      const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
+      kernel<<<(int)(g->batch < cap ? g->batch : cap), 32, 0, stream>>>(a);
+      g_launches.fetch_add(1);
+      MO_CUDA(cudaGetLastError());
+      return MO_OK;
+    };
+    switch (g->n / 8) {
+      case 4: return launch(mo::nls_linearize_dmma_kernel<4>);
+      case 5: return launch(mo::nls_linearize_dmma_kernel<5>);
+      case 6: return launch(mo::nls_linearize_dmma_kernel<6>);
+      case 7: return launch(mo::nls_linearize_dmma_kernel<7>);
+      default: return launch(mo::nls_linearize_dmma_kernel<8>);
+    }
+  }
   const long long cap = (long long)dev.sms * 32;
-  mo::nls_linearize_kernel<<<(int)(g->batch < cap ? g->batch : cap), 32, 0, static_cast<cudaStream_t>(cuda_stream)>>>(a);
+  mo::nls_linearize_kernel<<<(int)(g->batch < cap ? g->batch : cap), 32, 0, stream>>>(a);
   g_launches.fetch_add(1);
   MO_CUDA(cudaGetLastError());
   return MO_OK;

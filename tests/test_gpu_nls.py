@@ -102,6 +102,21 @@ def test_linearize_golden(dev, golden_nls, idx):
     assert np.all(np.triu(out.G.cpu().numpy().transpose(0, 2, 1), 1) == 0.0)  # residual_test.cc: upper triangle exactly 0
 
 
+@pytest.mark.parametrize("n,rc,cb,re", [(64, 128, 128, 16), (32, 40, 8, 8), (48, 50, 10, 0), (64, 16, 4, 3), (40, 72, 72, 5)])
+def test_linearize_dmma_vs_oracle(dev, oracle, n, rc, cb, re):
+    """n = 32 .. 64: the DMMA linearization kernel (nls_linearize_dmma.cuh) vs the C restatement of LinearizeAndFillQP /
+    UpdateHessian on the same bytes; residual_test.cc tolerance 1e-12 (relative to the magnitude of the sums), strict
+    upper triangle exactly 0, lambda only where > 0."""
+    from mini_opt_b200 import nls
+    a = N.random_linearize(500 + n + rc, n, rc, cb, re, batch=64)
+    want = oracle.nls_linearize("oracle", a)
+    out = nls.linearize_device(a, dev)
+    scale = float(np.abs(want.G).max())
+    for f in ("G", "c", "A_eq", "b_eq", "ineq_b_shifted", "errors"):
+        np.testing.assert_allclose(getattr(out, f).cpu().numpy(), getattr(want, f), atol=1e-12 * max(1.0, scale), rtol=0, err_msg=f)
+    assert np.all(np.triu(out.G.cpu().numpy().transpose(0, 2, 1), 1) == 0.0)
+
+
 def test_two_angle_chain(dev, golden_nls):
     """TestTwoAngleActuatorChain with inequalities (nonlinear_test.cc:925-960)."""
     ch, prm = N.two_angle_chain()
