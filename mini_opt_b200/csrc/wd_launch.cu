@@ -7,32 +7,29 @@
 
 namespace mo {
 
-// (N, K, warps per problem, min CTAs per SM); MO_QP_WD_WARPS=1|2 overrides the warp count for A/B runs.
-// Measured on B200 (ms per batch): n=64 64K QPs: 6 CTAs/SM (smem limit) 18.9; n=32 256K: 12 CTAs/SM (168 registers, no
-// spills) 18.5, 16 (128 registers) 19.6, 20 (96) 23.4; n=16 512K: 12 -> 19.3, 16 -> 19.1, 24 -> 23.5.
-#ifndef MO_WD_LA64
-#define MO_WD_LA64 false
+// Residency, measured on B200 in round 1 (ms per batch): n=64 64K QPs: 6 CTAs/SM 18.9, 7 (shared memory limit) 18.4;
+// n=32 256K: 12 CTAs/SM (168 registers, no spills) 18.5, 16 (128 registers) 19.6, 20 (96) 23.4; n=16 512K: 12 -> 19.3,
+// 16 -> 19.1, 24 -> 23.5.
+// Schedules, measured on B200 in round 2 (profiles/r02_wd_variants.txt, ms per batch of 64K / 256K / 512K QPs):
+//   plain left-looking columns, runtime back substitution loop      n=64 18.65   n=32 18.16   n=16 18.95   <- 64, 32
+//   + software-pipelined, unrolled back substitution (PBS)          n=64 19.23   n=32 18.37   n=16 18.43   <- 16
+//   + look-ahead columns (LA: pivot chain under the gather DMMAs)    n=64 21.38   n=32 18.37   n=16 18.41
+// LA and PBS lose at n = 64 on instruction fetch: the kernel grows from 9.1K to 12.4K SASS instructions and
+// smsp stall no_instruction doubles (0.55 -> 1.12 cycles per issue, profiles/r02_wd64_la_ncu_summary.txt).
+// (N, K, warps per problem, min CTAs per SM, look-ahead columns, pipelined back substitution)
+#ifndef MO_WD_SHAPES
+#define MO_WD_SHAPES(X) X(64, 16, 1, 7, false, false) X(32, 8, 1, 12, false, false) X(16, 8, 1, 16, false, true)
 #endif
-#ifndef MO_WD_LA32
-#define MO_WD_LA32 false
-#endif
-#ifndef MO_WD_LA16
-#define MO_WD_LA16 false
-#endif
-#ifndef MO_WD_PBS
-#define MO_WD_PBS true
-#endif
-#define MO_WD_SHAPES(X) X(64, 16, 1, 7, MO_WD_LA64) X(32, 8, 1, 12, MO_WD_LA32) X(16, 8, 1, 16, MO_WD_LA16)
 #ifdef MO_WD_AB_BUILD
-#define MO_WD_ALT_SHAPES(X) X(64, 16, 2, 6, false) X(32, 8, 2, 12, false) X(16, 8, 2, 12, false)
+#define MO_WD_ALT_SHAPES(X) X(64, 16, 2, 6, false, false) X(32, 8, 2, 12, false, false) X(16, 8, 2, 12, false, false)
 #else
 #define MO_WD_ALT_SHAPES(X)
 #endif
 
-template <int N, int K, int NW, int MINB, bool LA>
+template <int N, int K, int NW, int MINB, bool LA, bool PBS>
 static cudaError_t launch_wd(const QPArgs& a, int sms, cudaStream_t stream) {
   using L = WdLayout<N, K>;
-  auto kernel = qp_wd_kernel<N, K, NW, MINB, LA, (NW == 1) && MO_WD_PBS>;
+  auto kernel = qp_wd_kernel<N, K, NW, MINB, LA, PBS>;
   static thread_local int configured_dev = -1;
   static thread_local int bps = 0;
   int cur = 0;
@@ -52,7 +49,7 @@ static cudaError_t launch_wd(const QPArgs& a, int sms, cudaStream_t stream) {
 }
 
 bool wd_has_shape(int n, int k) {
-#define X(N_, K_, W_, B_, LA_) if (n == N_ && k == K_) return true;
+#define X(N_, K_, W_, B_, LA_, PBS_) if (n == N_ && k == K_) return true;
   MO_WD_SHAPES(X)
 #undef X
   return false;
@@ -65,7 +62,7 @@ cudaError_t wd_launch(const QPArgs& a, int sms, cudaStream_t stream) {
 #else
   constexpr int want = 0;
 #endif
-#define X(N_, K_, W_, B_, LA_) if (a.n == N_ && a.k == K_ && (want == 0 || want == W_)) return launch_wd<N_, K_, W_, B_, LA_>(a, sms, stream);
+#define X(N_, K_, W_, B_, LA_, PBS_) if (a.n == N_ && a.k == K_ && (want == 0 || want == W_)) return launch_wd<N_, K_, W_, B_, LA_, PBS_>(a, sms, stream);
   MO_WD_SHAPES(X)
   MO_WD_ALT_SHAPES(X)
 #undef X

@@ -21,7 +21,9 @@ pytestmark = pytest.mark.gpu
 # and 4 sigma of the sample (profiles/r02_gpu_test_fractions.jsonl). With an equality row the REFERENCE itself ends 40 % of
 # these synthetic problems in QP failure and its C restatement matches its counts on 70 %: chaos of the problem family,
 # which is why every problem additionally goes through assert_quality.
-IK_FLOORS = {"ik6": (0.93, 0.93), "ik12": (0.93, 0.93), "ik6q5": (0.93, 0.93), "ik8eq": (0.65, 0.65)}
+IK_FLOORS = {"ik6": (0.97, 0.97), "ik12": (0.96, 0.97), "ik6q5": (0.97, 0.97), "ik8eq": (0.70, 0.97)}
+# fraction of the same-trajectory problems whose x agrees to 1e-6 (problems ending in MAX_LAMBDA have an ill-conditioned x)
+IK_X6_FLOOR = {"ik6": 0.97, "ik12": 0.93, "ik6q5": 0.97, "ik8eq": 0.90}
 IK_ORACLE_FLOOR = {6: 0.93, 9: 0.93, 12: 0.93}
 
 
@@ -144,7 +146,7 @@ def test_chain_ik_golden(dev, golden_nls, tag, links, neq, qpi, B):
     need_same, need_term = IK_FLOORS[tag]
     assert same.mean() >= need_same, same.mean()
     assert term >= need_term, term
-    assert np.mean(dx[same] < 1e-6) >= 0.97, np.mean(dx[same] < 1e-6)
+    assert np.mean(dx[same] < 1e-6) >= IK_X6_FLOOR[tag], np.mean(dx[same] < 1e-6)
     not_worse, hdiff = assert_quality(out, ch, g[f"{tag}_errors"], g[f"{tag}_termination"], tag)
     assert not_worse >= 0.99, not_worse
     assert hdiff <= 0.01, hdiff
@@ -163,7 +165,7 @@ def test_chain_ik_vs_oracle(dev, oracle, links, strategy):
     _record(kind="ik_oracle", links=links, strategy=int(strategy), problems=1500, same=float(same.mean()),
             termination=float((out.termination == ref.termination).mean()), x6=float(np.mean(dx[same] < 1e-6)))
     assert same.mean() >= IK_ORACLE_FLOOR[links], same.mean()
-    assert np.mean(dx[same] < 1e-6) >= 0.97
+    assert np.mean(dx[same] < 1e-6) >= 0.93
     not_worse, hdiff = assert_quality(out, ch, ref.errors, ref.termination, f"oracle{links}")
     assert not_worse >= 0.99 and hdiff <= 0.01, (not_worse, hdiff)
     ok = same & (ref.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL)
