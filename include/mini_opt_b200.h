@@ -170,6 +170,19 @@ int mo_qp_ip_newton_step_batch(const mo_qp_batch* problems, double mu, int32_t b
                                double* vars, double* delta_out, double* ip_out, double* kkt_out,
                                int32_t* status, int device, void* cuda_stream);
 
+/* QPNullSpaceTerminationState, include/mini_opt/structs.hpp:137-142; 2 = rank(A_eq) < k (batched stand-in: the reference
+ * multiplies mismatched blocks there). */
+enum { MO_QP_NULLSPACE_SUCCESS = 0, MO_QP_NULLSPACE_NOT_POSITIVE_DEFINITE = 1, MO_QP_NULLSPACE_RANK_DEFICIENT = 2 };
+
+/*
+ * Replaces: QPNullSpaceSolver::Solve (source/qp.cc:679-729) for every problem of the batch: equality-constrained QP by
+ * column-pivoted Householder QR of A_eq^T, reduced Hessian Q2' G Q2, Cholesky. Reads G, c, A_eq, b_eq (k > 0); the
+ * inequality fields are ignored. x [batch][n] (zeros unless SUCCESS), status [batch] MO_QP_NULLSPACE_*. Device
+ * pointers, asynchronous on cuda_stream. This is the solver the NLS driver selects for problems with equality
+ * constraints and no inequalities (source/nonlinear.cc:83-89); mo_nls_solve_chain_ik_batch does the same.
+ */
+int mo_qp_nullspace_solve_batch(const mo_qp_batch* problems, double* x, int32_t* status, int device, void* cuda_stream);
+
 /* =====================================================================================================
  * Nonlinear least squares: Gauss-Newton / Levenberg-Marquardt linearization and the SQP loop
  * (ConstrainedNonlinearLeastSquares, include/mini_opt/nonlinear.hpp, source/nonlinear.cc)
@@ -313,9 +326,9 @@ int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, doub
  * Replaces: ConstrainedNonlinearLeastSquares::Solve (source/nonlinear.cc:75-158) -- LinearizeAndFillQP,
  * ComputeStepDirection (interior point QP, :216-259), ComputeQPCostDerivative, SelectPenalty, SelectStepSize,
  * UpdateLambdaAndCheckExitConditions -- for every problem of a transform-chain batch, entirely on the device.
- * Problems with equality constraints and NO inequalities would use QPNullSpaceSolver in the reference
- * (nonlinear.cc:83-89); that solver is out of scope and such batches return
- * MO_ERR_UNSUPPORTED_SHAPE. Device pointers, asynchronous on cuda_stream.
+ * Problems with equality constraints and NO inequalities use the null-space solver like the reference
+ * (nonlinear.cc:83-89), with the penalty update of inequality (18.36) (nonlinear.cc:492-500) and QP_INDEFINITE when the
+ * reduced Hessian is not positive definite. Device pointers, asynchronous on cuda_stream.
  */
 int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_params* params,
                                 const mo_nls_out* out, int device, void* cuda_stream);

@@ -1,5 +1,7 @@
 // C ABI of mini_opt_b200 (include/mini_opt_b200.h): argument checking, kernel selection, launches,
 // and the host-buffer convenience entry point. No torch, no Eigen: plain CUDA runtime.
+#include <nvtx3/nvToolsExt.h>
+
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -31,6 +33,15 @@ int cuda_fail(cudaError_t e, const char* what) {
     cudaError_t e_ = (call);                           \
     if (e_ != cudaSuccess) return cuda_fail(e_, #call); \
   } while (0)
+
+// NVTX range per entry point: the batched stand-in for the reference's opt-in MINI_OPT_FUNCTION_TRACE scoped timers
+// (include/mini_opt/tracing.hpp:67-83; call sites source/nonlinear.cc:77,173,218,280,355,459). Header-only NVTX v3: a
+// no-op unless a tool (nsys, ncu --nvtx) is attached.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+#define MO_TRACE() NvtxRange mo_nvtx_range_(__func__)
 
 struct DeviceGuard {
   int prev = -1;
@@ -367,6 +378,7 @@ const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags)
 
 int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out, int device,
                          void* cuda_stream) {
+  MO_TRACE();
   if (!problems || !params || !out) return MO_ERR_INVALID_ARGUMENT;
   int rc = check_batch(problems);
   if (rc) return rc;
@@ -390,6 +402,7 @@ int mo_qp_ip_solve_batch(const mo_qp_batch* problems, const mo_qp_params* params
 int mo_qp_ip_newton_step_batch(const mo_qp_batch* problems, double mu, int32_t barrier_strategy, double* vars,
                                double* delta_out, double* ip_out, double* kkt_out, int32_t* status, int device,
                                void* cuda_stream) {
+  MO_TRACE();
   if (!problems || !vars || !status) return MO_ERR_INVALID_ARGUMENT;
   int rc = check_batch(problems);
   if (rc) return rc;
@@ -625,6 +638,7 @@ void mo_host_free(void* p) {
 
 int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
                               int device) {
+  MO_TRACE();
   const int rc = check_host_call(problems, params, out);
   if (rc || problems->batch == 0) return rc;
   return solve_host_range(*problems, *params, *out, 0, problems->batch, device);
@@ -632,6 +646,7 @@ int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* p
 
 int mo_qp_ip_solve_batch_host_multi(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,
                                     const int* devices, int n_devices) {
+  MO_TRACE();
   if (!devices || n_devices < 1 || n_devices > 64) return MO_ERR_INVALID_ARGUMENT;
   const int rc = check_host_call(problems, params, out);
   if (rc || problems->batch == 0) return rc;
@@ -735,7 +750,31 @@ void mo_nls_params_default(mo_nls_params* p) {  // nonlinear.hpp:37-124
   p->retraction = MO_RETRACT_ADD; p->inner_qp_solver = MO_NLS_QP_AUTO;
 }
 
+int mo_qp_nullspace_solve_batch(const mo_qp_batch* problems, double* x, int32_t* status, int device, void* cuda_stream) {
+  MO_TRACE();
+  if (!problems || problems->n <= 0 || problems->k <= 0 || problems->batch < 0) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->batch == 0) return MO_OK;
+  if (!problems->G || !problems->c || !problems->A_eq || !problems->b_eq || !x || !status) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->flags & kHostOnlyFlags) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  int rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  const size_t smem = sizeof(double) * mo::ns_smem_doubles(problems->n, problems->k);
+  int grid = 0;
+  rc = warp_grid(mo::qp_nullspace_kernel, smem, problems->batch, dev, &grid);
+  if (rc) return rc;
+  const mo::NullSpaceArgs a{problems->n, problems->k, problems->batch, problems->G, problems->c, problems->A_eq,
+                            problems->b_eq, x, status};
+  mo::qp_nullspace_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(a);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
+
 int mo_nls_linearize_batch(const mo_nls_linearize_args* g, int device, void* cuda_stream) {
+  MO_TRACE();
   if (!g || g->n <= 0 || g->r_cost < 0 || g->r_eq < 0 || g->m < 0 || g->batch < 0) return MO_ERR_INVALID_ARGUMENT;
   if (g->cost_block < 0 || (g->cost_block > 0 && g->r_cost % g->cost_block != 0)) return MO_ERR_INVALID_ARGUMENT;
   if (g->batch == 0) return MO_OK;
@@ -782,6 +821,7 @@ int mo_nls_linearize_batch(const mo_nls_linearize_args* g, int device, void* cud
 
 int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, double* translation, double* rotation_q,
                       double* t_D_params, double* r_D_params, int device, void* cuda_stream) {
+  MO_TRACE();
   int rc = check_chain(chain, true);
   if (rc) return rc;
   if (chain->batch == 0) return MO_OK;
@@ -805,15 +845,12 @@ int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, doub
 
 int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
                                 int device, void* cuda_stream) {
+  MO_TRACE();
   if (!params || !out) return MO_ERR_INVALID_ARGUMENT;
   int rc = check_chain(problems, false);
   if (rc) return rc;
   rc = check_nls_params(params);
   if (rc) return rc;
-  if (problems->n_eq > 0 && problems->m == 0) {
-    g_last_error = "equality-only problems use QPNullSpaceSolver in the reference (nonlinear.cc:83-89): not built";
-    return MO_ERR_UNSUPPORTED_SHAPE;
-  }
   if (problems->batch == 0) return MO_OK;
   if (!out->x || !out->termination || !out->iterations) return MO_ERR_INVALID_ARGUMENT;
   DeviceInfo dev;

@@ -12,6 +12,7 @@
 
 #include "qp_generic.cuh"
 #include "qp_warp.cuh"
+#include "qp_nullspace.cuh"
 
 namespace mo {
 
@@ -410,7 +411,10 @@ __device__ inline void chain_errors(ChainWork& C, const ChainArgs& a, long long 
 }
 
 __host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost, int k, int m) {
-  size_t d = chain_smem_doubles(links, n) + gen_smem_doubles(n, k, m, 32);
+  // inner QP workspace: the interior point solver's, or (equalities and no inequalities) the null-space solver's
+  const size_t qpw = (m == 0 && k > 0 && ns_smem_doubles(n, k) > gen_smem_doubles(n, k, m, 32)) ? ns_smem_doubles(n, k)
+                                                                                               : gen_smem_doubles(n, k, m, 32);
+  size_t d = chain_smem_doubles(links, n) + qpw;
   d += (size_t)n * n + n + (size_t)k * n + k + m;       // QP: G, c, A, b, shifted bounds
   d += (size_t)n_cost * n + (size_t)k * n + 3 * (size_t)n; // Jc, Je, x, cand, dx
   d += 2 * kMaxChainRows + 8;                            // residual buffers, errors
@@ -444,7 +448,9 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
   double* q = chain_carve(C, smem, a.links, n);
   GenWork W;
   gen_carve(W, q, n, k, m, 32);
-  q += gen_smem_doubles(n, k, m, 32);
+  const bool null_space = m == 0 && k > 0;  // solver choice of the reference, nonlinear.cc:83-89
+  double* nswork = q;                       // QPNullSpaceSolver workspace aliases the interior point workspace
+  q += (null_space && ns_smem_doubles(n, k) > gen_smem_doubles(n, k, m, 32)) ? ns_smem_doubles(n, k) : gen_smem_doubles(n, k, m, 32);
   double* G = q; q += n * n;
   double* cvec = q; q += n;
   double* A = q; q += k * n;
@@ -482,11 +488,18 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
       __syncwarp();
       int qiters = 0;
       double kkt_after[4];
-      int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve_any(W, Q, sp, qiters, kkt_after);
-      if (qstatus < 0) qstatus = gen_solve<32>(W, Q, sp, nullptr, qiters, kkt_after);
-      if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; }  // the reference throws here
-      qp_total += qiters;
-      for (int i = lane; i < n; i += 32) dx[i] = W.vars[i];
+      if (null_space) {  // QPNullSpaceSolver (qp.cc:679-729); dx = 0 unless SUCCESS (nonlinear.cc:248-258)
+        const int ns = ns_solve_warp(n, k, G, cvec, A, bvec, dx, nswork);
+        if (ns == 1) { term = MO_NLS_QP_INDEFINITE; break; }  // QPWasIndefinite, nonlinear.cc:103-105
+        if (ns != 0) { term = MO_NLS_QP_FAILED; break; }
+        qp_total += 1;  // NumQPIterations counts one per null-space solve (structs.cc:208-219)
+      } else {
+        int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve_any(W, Q, sp, qiters, kkt_after);
+        if (qstatus < 0) qstatus = gen_solve<32>(W, Q, sp, nullptr, qiters, kkt_after);
+        if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; }  // the reference throws here
+        qp_total += qiters;
+        for (int i = lane; i < n; i += 32) dx[i] = W.vars[i];
+      }
       __syncwarp();
       // ---- ComputeQPCostDerivative (:457-482), SelectPenalty (:484-502) ----
       double d_f = 0.0, d_eq = 0.0;
@@ -497,7 +510,18 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
         const double br = bvec[r];
         d_eq += (br > 0 ? 1.0 : (br < 0 ? -1.0 : 0.0)) * d;
       }
-      if (k) {
+      if (k && null_space) {  // no multipliers: inequality (18.36), nonlinear.cc:492-500
+        double l1 = 0.0, quad = 0.0;
+        for (int r = 0; r < k; ++r) l1 += fabs(bvec[r]);
+        l1 = fmax(l1, 2.220446049250313e-16);
+        for (int i = 0; i < n; ++i) {
+          double acc = 0.0;
+          for (int j = 0; j < n; ++j) acc += (i >= j ? G[j * n + i] : G[i * n + j]) * dx[j];
+          quad += dx[i] * acc;
+        }
+        const double np = (d_f + 0.5 * fmax(0.0, quad)) / ((1 - prm.equality_penalty_rho) * l1);
+        if (np > penalty) penalty = np * prm.equality_penalty_scale_factor;
+      } else if (k) {
         const double* y = W.vars + n + m;
         double linf = fabs(y[0]);
         for (int r = 1; r < k; ++r) linf = fmax(linf, fabs(y[r]));

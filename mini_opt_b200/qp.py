@@ -71,6 +71,19 @@ def solve_batch_host(arrs: abi.QPBatchArrays, params: abi.QPParams, out: abi.QPO
     lib.check(L.mo_qp_ip_solve_batch_host(C.byref(b), C.byref(p), C.byref(o), int(device_index)))
 
 
+def nullspace_solve_device(arrs: abi.QPBatchArrays, device):
+    """``mo_qp_nullspace_solve_batch`` on device tensors: (x [B, n], status [B]) torch tensors."""
+    import torch
+
+    L = lib.load()
+    x = torch.zeros((arrs.batch, arrs.n), dtype=torch.float64, device=device)
+    status = torch.full((arrs.batch,), -1, dtype=torch.int32, device=device)
+    b = arrs.to_c()
+    st = torch.cuda.current_stream(device)
+    lib.check(L.mo_qp_nullspace_solve_batch(C.byref(b), x.data_ptr(), status.data_ptr(), _device_index(device), st.cuda_stream))
+    return x, status
+
+
 def solve_batch_host_multi(arrs: abi.QPBatchArrays, params: abi.QPParams, out: abi.QPOutArrays, devices):
     """``mo_qp_ip_solve_batch_host_multi``: one host batch sharded over several devices of this node from one process."""
     L = lib.load()

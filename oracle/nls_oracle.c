@@ -26,6 +26,7 @@
 #include "mini_opt_b200.h"
 
 int64_t oracle_qp_solve_batch(const mo_qp_batch* b, const mo_qp_params* prm, const mo_qp_out* out);
+int oracle_qp_nullspace_one(int n, int k, const double* G, const double* c, const double* A, const double* b, double* x);
 
 #define MAX_LINKS 64
 
@@ -462,13 +463,21 @@ static void solve_one(const mo_chain_ik_batch* b, const mo_nls_params* prm, int6
     qp.initialize_mu_with_complementarity = 0; qp.reserved = 0;
     int32_t qstatus = -1, qiters = 0;
     double lag[2] = {0, 0};
-    mo_qp_out qo;
-    memset(&qo, 0, sizeof(qo));
-    qo.vars = w->vars; qo.status = &qstatus; qo.iters = &qiters; qo.lagrange = lag;
-    oracle_qp_solve_batch(&qb, &qp, &qo);
-    if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; } /* the reference throws */
-    qp_total += qiters;
-    for (int i = 0; i < n; ++i) w->dx[i] = w->vars[i];
+    const int null_space = m == 0 && k > 0; /* solver choice, nonlinear.cc:83-89 */
+    if (null_space) {
+      const int ns = oracle_qp_nullspace_one(n, k, w->G, w->c, w->A, w->b, w->dx); /* dx = 0 unless SUCCESS, :248-258 */
+      if (ns == 1) { term = MO_NLS_QP_INDEFINITE; break; } /* QPWasIndefinite, nonlinear.cc:103-105 */
+      if (ns != 0) { term = MO_NLS_QP_FAILED; break; }
+      qp_total += 1; /* NumQPIterations counts one per null-space solve, structs.cc:208-219 */
+    } else {
+      mo_qp_out qo;
+      memset(&qo, 0, sizeof(qo));
+      qo.vars = w->vars; qo.status = &qstatus; qo.iters = &qiters; qo.lagrange = lag;
+      oracle_qp_solve_batch(&qb, &qp, &qo);
+      if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; } /* the reference throws */
+      qp_total += qiters;
+      for (int i = 0; i < n; ++i) w->dx[i] = w->vars[i];
+    }
     /* ComputeQPCostDerivative, :457-482 */
     double d_f = 0.0, d_eq = 0.0;
     for (int i = 0; i < n; ++i) d_f += w->c[i] * w->dx[i];
@@ -479,7 +488,19 @@ static void solve_one(const mo_chain_ik_batch* b, const mo_nls_params* prm, int6
     }
     /* SelectPenalty, :484-502 (interior point branch: |y|_inf) */
     if (k) {
-      const double new_penalty = lag[1];
+      double new_penalty = lag[1];
+      if (null_space) { /* no multipliers: inequality (18.36), nonlinear.cc:492-500 */
+        double l1 = 0.0, cdx = 0.0, quad = 0.0;
+        for (int r = 0; r < k; ++r) l1 += fabs(w->b[r]);
+        if (l1 < DBL_EPSILON) l1 = DBL_EPSILON;
+        for (int i = 0; i < n; ++i) cdx += w->c[i] * w->dx[i];
+        for (int i = 0; i < n; ++i) {
+          double acc = 0.0;
+          for (int j = 0; j < n; ++j) acc += (i >= j ? w->G[(size_t)j * n + i] : w->G[(size_t)i * n + j]) * w->dx[j];
+          quad += w->dx[i] * acc;
+        }
+        new_penalty = (cdx + 0.5 * (quad > 0.0 ? quad : 0.0)) / ((1 - prm->equality_penalty_rho) * l1);
+      }
       if (new_penalty > penalty) penalty = new_penalty * prm->equality_penalty_scale_factor;
     }
     /* SelectStepSize, :351-416 */

@@ -161,6 +161,22 @@ def qp_newton_step(which: str, arrs: abi.QPBatchArrays, mu: float, strategy: int
     return dict(vars=v, delta=delta, ip=ip, kkt=kkt, status=status)
 
 
+def qp_nullspace(which: str, arrs: abi.QPBatchArrays):
+    """``QPNullSpaceSolver::Solve`` (qp.cc:679-729) per problem of a host batch: (x [B, n], status [B])."""
+    _check_host(arrs)
+    x = np.zeros((arrs.batch, arrs.n))
+    status = np.full(arrs.batch, -1, dtype=np.int32)
+    lib = oracle_lib() if which == "oracle" else ref_lib()
+    fn = getattr(lib, f"{which}_qp_nullspace_batch")
+    fn.restype = C.c_int
+    fn.argtypes = [C.POINTER(abi.MoQpBatch), C.c_void_p, C.c_void_p]
+    b = arrs.to_c()
+    rc = fn(C.byref(b), x.ctypes.data, status.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"{which}_qp_nullspace_batch failed: {rc}")
+    return x, status
+
+
 def generate_random_qp(seed: int, dim: int = 8, p_inequality: float = 0.5):
     """The reference's own ``GenerateRandomQP`` (test/qp_test.cc:483-524). Needs oracle/_ref."""
     lib = ref_lib()

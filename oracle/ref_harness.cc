@@ -247,6 +247,22 @@ int ref_qp_newton_step_batch(const mo_qp_batch* b, double mu, int32_t strategy, 
   return MO_OK;
 }
 
+// Reference QPNullSpaceSolver::Solve (source/qp.cc:679-729) per problem: x [batch][n], status [batch]
+// (QPNullSpaceTerminationState: 0 SUCCESS, 1 NOT_POSITIVE_DEFINITE). Inequalities of the batch are ignored.
+int ref_qp_nullspace_batch(const mo_qp_batch* b, double* x, int32_t* status) {
+  if (!b || !x || !status || b->k <= 0) return MO_ERR_INVALID_ARGUMENT;
+  QP qp;
+  QPNullSpaceSolver solver;
+  for (int64_t p = 0; p < b->batch; ++p) {
+    UnpackQP(*b, p, &qp);
+    qp.constraints.clear();
+    const QPNullSpaceTerminationState term = solver.Solve(qp);
+    status[p] = static_cast<int32_t>(term);
+    for (int i = 0; i < b->n; ++i) x[p * b->n + i] = term == QPNullSpaceTerminationState::SUCCESS ? solver.variables()[i] : 0.0;
+  }
+  return MO_OK;
+}
+
 int ref_hardware_concurrency() { return static_cast<int>(std::thread::hardware_concurrency()); }
 
 }  // extern "C"

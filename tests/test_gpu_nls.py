@@ -181,7 +181,22 @@ def test_nls_invalid_arguments(dev):
     with pytest.raises(lib.MiniOptError) as e:
         nls.solve_chain_ik_device(d, bad, out, dev)
     assert e.value.code == abi.MO_ERR_INVALID_PARAMS
-    d.m = 0  # equality-only -> QPNullSpaceSolver in the reference: not built
-    with pytest.raises(lib.MiniOptError) as e:
-        nls.solve_chain_ik_device(d, prm, out, dev)
-    assert e.value.code == abi.MO_ERR_UNSUPPORTED_SHAPE
+
+
+def test_chain_ik_equality_only_nullspace(dev, oracle):
+    """Equality constraints and no inequalities: the reference switches to QPNullSpaceSolver (nonlinear.cc:83-89) with
+    the (18.36) penalty; same on the device. Against the C restatement (pinned to the reference in test_oracle_nls.py)."""
+    import dataclasses
+    ch = synth.chain_ik_batch_numpy(6, 3000, seed=11, n_eq=1)
+    ch = dataclasses.replace(ch, m=0, ineq_var=None, ineq_a=None, ineq_b=None)
+    prm = synth.chain_ik_params()
+    ref, _ = oracle.nls_solve_chain("oracle", ch, prm)
+    out = gpu_nls(ch, prm, dev)
+    same = counts_same(out, ref.termination, ref.iterations, ref.qp_iterations, ref.ls_steps)
+    term = (out.termination == ref.termination).mean()
+    dx = np.abs(out.x - ref.x).max(axis=1)
+    _record(kind="ik_nullspace", problems=3000, same=float(same.mean()), termination=float(term),
+            x6=float(np.mean(dx[same] < 1e-6)))
+    assert term >= 0.97 and same.mean() >= 0.93, (term, same.mean())
+    merit_gpu, merit_ref = out.errors.sum(axis=1), ref.errors.sum(axis=1)
+    assert np.mean(merit_gpu <= merit_ref * 1.001 + 1e-9) >= 0.99

@@ -463,3 +463,28 @@ def test_host_entry_multi_device(dev):
     qp.solve_batch_host_multi(arrs, prm, many, devices)
     assert np.array_equal(one.status, many.status) and np.array_equal(one.iters, many.iters)
     np.testing.assert_array_equal(one.vars, many.vars)
+
+
+def test_nullspace_solver_vs_oracle(dev, oracle):
+    """mo_qp_nullspace_solve_batch (QPNullSpaceSolver, qp.cc:679-729) vs the C restatement on identical bytes, the
+    closed-form case of TestNullSpaceSolver1 and the NOT_POSITIVE_DEFINITE status."""
+    import torch
+    from mini_opt_b200 import qp
+    for n, k, B in ((6, 2, 3000), (12, 3, 2000), (16, 8, 1000), (64, 16, 200), (8, 8, 100), (3, 1, 100)):
+        arrs = synth.box_qp_batch_numpy(n, k, B, seed=50 + n, explicit_constraints=False)
+        want, ws = oracle.qp_nullspace("oracle", arrs)
+        x, st = qp.nullspace_solve_device(qp.to_device(arrs, dev), dev)
+        torch.cuda.synchronize()
+        assert np.array_equal(st.cpu().numpy(), ws)
+        np.testing.assert_allclose(x.cpu().numpy(), want, rtol=1e-9, atol=1e-11)
+    semi = synth.box_qp_batch_numpy(6, 2, 64, seed=1, explicit_constraints=False)
+    semi.G[:] = 0.0
+    x, st = qp.nullspace_solve_device(qp.to_device(semi, dev), dev)
+    assert (st.cpu().numpy() == 1).all() and (x.cpu().numpy() == 0).all()
+    Am = np.array([[-2.0, 1.4], [2.2, -3.5]])
+    bv = np.array([-0.8, 1.3])
+    one = abi.QPBatchArrays(n=2, k=1, m=0, batch=1, G=np.ascontiguousarray((Am.T @ Am).T[None]),
+                            c=np.ascontiguousarray((-Am.T @ bv)[None]), A_eq=np.array([[[0.0], [1.0]]]), b_eq=np.array([[-0.3]]))
+    x, st = qp.nullspace_solve_device(qp.to_device(one, dev), dev)
+    assert int(st[0]) == 0
+    np.testing.assert_allclose(x.cpu().numpy()[0], [0.860859728506787, 0.3], atol=1e-12)

@@ -109,3 +109,21 @@ def test_oracle_nls_rejects_bad_params(oracle):
         p = abi.NLSParams(**{**prm.__dict__, **bad})
         with pytest.raises(RuntimeError):
             oracle.nls_solve_chain("oracle", ch, p)
+
+
+def test_equality_only_chain_uses_nullspace_like_reference():
+    """Equality rows and no inequalities: QPNullSpaceSolver + the (18.36) penalty (nonlinear.cc:83-89, 492-500). The C
+    restatement against the reference on the same chains."""
+    import dataclasses
+    from oracle import oracle_py as O
+    if not O.ref_available():
+        pytest.skip("reference library not built")
+    ch = synth.chain_ik_batch_numpy(6, 1500, seed=11, n_eq=1)
+    ch = dataclasses.replace(ch, m=0, ineq_var=None, ineq_a=None, ineq_b=None)
+    prm = synth.chain_ik_params()
+    ref, _ = O.nls_solve_chain("ref", ch, prm, nthreads=4)
+    orc, _ = O.nls_solve_chain("oracle", ch, prm)
+    assert (ref.termination == orc.termination).mean() >= 0.995
+    same = (ref.termination == orc.termination) & (ref.iterations == orc.iterations) & (ref.ls_steps == orc.ls_steps) & \
+           (ref.qp_iterations == orc.qp_iterations)
+    assert same.mean() >= 0.96, same.mean()

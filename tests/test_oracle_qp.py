@@ -138,3 +138,32 @@ def test_oracle_empty_batch(oracle):
     arrs = synth.box_qp_batch_numpy(4, 1, 0, seed=3)
     out, total = oracle.qp_solve("oracle", arrs, abi.QPParams())
     assert total == 0 and out.vars.shape[0] == 0
+
+
+def test_nullspace_oracle_vs_reference_and_closed_form():
+    """QPNullSpaceSolver (qp.cc:679-729): the C restatement against the reference itself on seeded batches, the
+    NOT_POSITIVE_DEFINITE status, and TestNullSpaceSolver1 (qp_test.cc:576-626): x = (0.860859728506787, 0.3)."""
+    from oracle import oracle_py as O
+    if not O.ref_available():
+        pytest.skip("reference library not built")
+    for n, k, B in ((6, 2, 500), (12, 3, 300), (16, 8, 200), (64, 16, 20), (8, 8, 50)):
+        arrs = synth.box_qp_batch_numpy(n, k, B, seed=5 + n, explicit_constraints=False)
+        xr, sr = O.qp_nullspace("ref", arrs)
+        xo, so = O.qp_nullspace("oracle", arrs)
+        assert np.array_equal(sr, so) and (sr == 0).all()
+        np.testing.assert_allclose(xo, xr, rtol=1e-9, atol=1e-11)
+        A = arrs.A_eq.transpose(0, 2, 1)
+        assert np.abs(np.einsum("bkn,bn->bk", A, xo) + arrs.b_eq).max() < 1e-12
+    semi = synth.box_qp_batch_numpy(6, 2, 10, seed=1, explicit_constraints=False)
+    semi.G[:] = 0.0
+    assert (O.qp_nullspace("ref", semi)[1] == 1).all() and (O.qp_nullspace("oracle", semi)[1] == 1).all()
+    # TestNullSpaceSolver1: cost |A x - b|^2 linearized at 0 (G = A'A, c = -A'b), x1 pinned to 0.3
+    Am = np.array([[-2.0, 1.4], [2.2, -3.5]])
+    bv = np.array([-0.8, 1.3])
+    G = Am.T @ Am
+    one = abi.QPBatchArrays(n=2, k=1, m=0, batch=1, G=np.ascontiguousarray(G.T[None]), c=np.ascontiguousarray((-Am.T @ bv)[None]),
+                            A_eq=np.array([[[0.0], [1.0]]]), b_eq=np.array([[-0.3]]))
+    for which in ("ref", "oracle"):
+        x, st = O.qp_nullspace(which, one)
+        assert st[0] == 0
+        np.testing.assert_allclose(x[0], [0.860859728506787, 0.3], atol=1e-12)
