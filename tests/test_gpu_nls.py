@@ -21,10 +21,13 @@ pytestmark = pytest.mark.gpu
 # and 4 sigma of the sample (profiles/r02_gpu_test_fractions.jsonl). With an equality row the REFERENCE itself ends 40 % of
 # these synthetic problems in QP failure and its C restatement matches its counts on 70 %: chaos of the problem family,
 # which is why every problem additionally goes through assert_quality.
-IK_FLOORS = {"ik6": (0.97, 0.97), "ik12": (0.96, 0.97), "ik6q5": (0.97, 0.97), "ik8eq": (0.70, 0.97)}
+IK_FLOORS = {"ik6": (0.99, 0.99), "ik12": (0.985, 0.985), "ik6q5": (0.99, 0.99), "ik8eq": (0.75, 0.985)}
 # fraction of the same-trajectory problems whose x agrees to 1e-6 (problems ending in MAX_LAMBDA have an ill-conditioned x)
-IK_X6_FLOOR = {"ik6": 0.97, "ik12": 0.93, "ik6q5": 0.97, "ik8eq": 0.90}
-IK_ORACLE_FLOOR = {6: 0.93, 9: 0.93, 12: 0.93}
+IK_X6_FLOOR = {"ik6": 0.985, "ik12": 0.96, "ik6q5": 0.99, "ik8eq": 0.93}
+# measured (profiles/r02_gpu_test_fractions.jsonl): same 1.0 / 0.9873 / 0.984, x6 0.9947 / 0.9770 / 0.9885, not worse 1.0 / 0.9893 / 0.9967
+IK_ORACLE_FLOOR = {6: 0.995, 9: 0.983, 12: 0.98}
+IK_ORACLE_X6 = {6: 0.99, 9: 0.972, 12: 0.984}
+IK_ORACLE_NOT_WORSE = {6: 0.997, 9: 0.985, 12: 0.993}
 
 
 @pytest.fixture(scope="module")
@@ -165,9 +168,9 @@ def test_chain_ik_vs_oracle(dev, oracle, links, strategy):
     _record(kind="ik_oracle", links=links, strategy=int(strategy), problems=1500, same=float(same.mean()),
             termination=float((out.termination == ref.termination).mean()), x6=float(np.mean(dx[same] < 1e-6)))
     assert same.mean() >= IK_ORACLE_FLOOR[links], same.mean()
-    assert np.mean(dx[same] < 1e-6) >= 0.93
+    assert np.mean(dx[same] < 1e-6) >= IK_ORACLE_X6[links]
     not_worse, hdiff = assert_quality(out, ch, ref.errors, ref.termination, f"oracle{links}")
-    assert not_worse >= 0.99 and hdiff <= 0.01, (not_worse, hdiff)
+    assert not_worse >= IK_ORACLE_NOT_WORSE[links] and hdiff <= 0.005, (not_worse, hdiff)
     ok = same & (ref.termination == abi.MO_NLS_SATISFIED_ABSOLUTE_TOL)
     np.testing.assert_allclose(out.errors[ok], ref.errors[ok], atol=1e-9)
 
@@ -197,6 +200,6 @@ def test_chain_ik_equality_only_nullspace(dev, oracle):
     dx = np.abs(out.x - ref.x).max(axis=1)
     _record(kind="ik_nullspace", problems=3000, same=float(same.mean()), termination=float(term),
             x6=float(np.mean(dx[same] < 1e-6)))
-    assert term >= 0.97 and same.mean() >= 0.93, (term, same.mean())
+    assert term >= 0.996 and same.mean() >= 0.98, (term, same.mean())  # measured 0.9997 / 0.9837
     merit_gpu, merit_ref = out.errors.sum(axis=1), ref.errors.sum(axis=1)
     assert np.mean(merit_gpu <= merit_ref * 1.001 + 1e-9) >= 0.99

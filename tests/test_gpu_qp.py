@@ -149,10 +149,10 @@ def test_box_synth_vs_reference_golden(dev, golden_box, n, gname, guess, explici
 
     class R:
         status, iters, vars = g[f"{tag}_status"], g[f"{tag}_iters"], g[f"{tag}_vars"]
-    if gname == "naive":
-        compare(out, R, n)
-    else:
-        compare(out, R, n, min_same=0.97, min_x=0.97, min_status=0.99)
+    if gname == "naive" or n > 8:
+        compare(out, R, n)  # identical status, iteration count and x (1e-9) on every problem
+    else:  # n = 8, clamped starts: measured same 0.9883 (3 of 256), x 0.996, status 1.0
+        compare(out, R, n, min_same=0.98, min_x=0.99, min_status=1.0)
     ok = out.iters == R.iters
     np.testing.assert_allclose(out.kkt_final[ok], g[f"{tag}_kkt"][ok], rtol=1e-6, atol=KKT_ATOL)
     tight = ok & (gu.rel_x_err(out.vars, R.vars, n) < X_RTOL)  # multipliers of the non-chaotic trajectories
@@ -172,9 +172,12 @@ def test_box_synth_vs_oracle(dev, oracle, n, k, B, guess):
     ref, _ = oracle.qp_solve("oracle", arrs, prm)
     out = gpu_solve(arrs, prm, dev)
     if guess == abi.MO_GUESS_NAIVE:
-        same, rel = compare(out, ref, n, min_same=0.999, min_x=0.999)
+        same, rel = compare(out, ref, n)  # measured 1.0 on every shape
     else:
-        same, rel = compare(out, ref, n, min_same=0.97, min_x=0.97, min_status=0.99)
+        # clamped starts (s = 1e-9, z = 1e9). Measured on B200 (profiles/r02_gpu_test_fractions.jsonl), floors = measured - 0.3 %:
+        # (8,2) same 0.99575 status 0.9998 x 0.99905; (6,2) same 0.9795 status 0.999 x 0.99847; every other shape 1.0
+        floors = {(8, 2): (0.992, 0.9968, 0.996), (6, 2): (0.976, 0.996, 0.995)}.get((n, k), (0.997, 0.999, 0.997))
+        same, rel = compare(out, ref, n, min_same=floors[0], min_status=floors[1], min_x=floors[2])
     np.testing.assert_allclose(out.kkt_final[same], ref.kkt_final[same], rtol=1e-6, atol=KKT_ATOL)
 
 
@@ -186,7 +189,7 @@ def test_barrier_strategies_vs_oracle(dev, oracle, strategy):
     prm.decrease_mu_only_on_small_error = strategy == abi.MO_BARRIER_FIXED_DECREASE
     ref, _ = oracle.qp_solve("oracle", arrs, prm, log=True)
     out = gpu_solve(arrs, prm, dev, log=True)
-    same, _ = compare(out, ref, 8, min_same=0.99, min_x=0.99)
+    same, _ = compare(out, ref, 8)  # NAIVE start: measured 1.0
     p = int(np.flatnonzero(same)[0])
     its = int(out.iters[p])
     assert_log_close(out.iter_log[p, :its], ref.iter_log[p, :its], cols=14)
@@ -205,7 +208,7 @@ def test_user_provided_guess_and_flags(dev, oracle):
     prm.initialize_mu_with_complementarity = True
     ref, _ = oracle.qp_solve("oracle", arrs, prm, user_vars=uv)
     out = gpu_solve(arrs, prm, dev, user_vars=uv)
-    compare(out, ref, 8, min_same=0.995, min_x=0.995)
+    compare(out, ref, 8)  # interior user start: measured 1.0
 
 
 def test_max_iterations_and_failures(dev, oracle):
@@ -417,7 +420,7 @@ def test_dmma_kernels_log_and_user_guess_vs_oracle(dev, oracle, n, k, dmma_varia
     prm.initialize_mu_with_complementarity = True
     ref, _ = oracle.qp_solve("oracle", arrs, prm, user_vars=uv)
     out = gpu_solve(arrs, prm, dev, user_vars=uv)
-    compare(out, ref, n, min_same=0.99, min_x=0.99)
+    compare(out, ref, n)  # interior user start on the DMMA kernels: measured 1.0
 
 
 def test_host_entry_compact_formats(dev, oracle):
