@@ -183,6 +183,22 @@ enum { MO_QP_NULLSPACE_SUCCESS = 0, MO_QP_NULLSPACE_NOT_POSITIVE_DEFINITE = 1, M
  */
 int mo_qp_nullspace_solve_batch(const mo_qp_batch* problems, double* x, int32_t* status, int device, void* cuda_stream);
 
+/*
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation). Same contract and results as
+ * mo_qp_nullspace_solve_batch, but the per-warp workspace (QR factors, Q, reduced Hessian: O(n^2) doubles per resident
+ * problem) lives in ONE file-scope device array of 32 MiB instead of dynamic shared memory, and the call makes no
+ * cudaMalloc / cudaFree / allocating library call. Limits and caveats:
+ *   - n <= MO_NOALLOC_MAX_N (else MO_ERR_UNSUPPORTED_SHAPE with a message in mo_last_error_string()); any batch size;
+ *   - every GPU that loads the library holds the 32 MiB array until the process exits;
+ *   - every call on a device shares the array: calls that OVERLAP on the GPU (different streams, no ordering) race;
+ *     order them on one stream or with events. Nothing in it needs to start at zero (every word is written before it is
+ *     read), so a call does not clear it and it keeps the last call's contents.
+ */
+#define MO_NOALLOC_MAX_N 128
+int mo_qp_nullspace_solve_batch_noalloc(const mo_qp_batch* problems, double* x, int32_t* status, int device,
+                                        void* cuda_stream);
+
 /* =====================================================================================================
  * Nonlinear least squares: Gauss-Newton / Levenberg-Marquardt linearization and the SQP loop
  * (ConstrainedNonlinearLeastSquares, include/mini_opt/nonlinear.hpp, source/nonlinear.cc)

@@ -41,6 +41,7 @@ MO_QP_FLAG_BOX_PAIRS = 1
 MO_QP_FLAG_PACKED_G = 2
 MO_QP_FLAG_UNIFORM_BOX = 4
 MO_QP_ITER_LOG_STRIDE = 14
+MO_NOALLOC_MAX_N = 128
 
 _dp = C.c_void_p  # data pointers are passed as raw addresses (host or device)
 

@@ -896,3 +896,78 @@ extern "C" int mo_debug_read_trace(long long* out, int cap) {
   return n;
 }
 #endif
+
+// ---------------------------------------------------------------------------------------------
+// No-allocation entry point (no counterpart in the reference).
+// Variant of qp_nullspace_kernel whose per-warp workspace (QR, Q, G Z, Z'G Z, vectors: ns_smem_doubles(n, k) doubles)
+// lives in a file-scope device array instead of dynamic shared memory: callers under CUDA graph capture or in loops
+// that may not call cudaMalloc get a fixed footprint, and problems whose workspace exceeds the 227 KB of shared memory
+// (n > ~100) can be solved at all. Every GPU that loads the library holds the array (32 MiB) until exit.
+// ---------------------------------------------------------------------------------------------
+namespace mo {
+constexpr size_t kNoAllocScratchBytes = size_t(32) << 20;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// `scratch`: the DEVICE address of g_noalloc_scratch obtained with cudaGetSymbolAddress (the host-side name of the array
+// is only a stand-in); block b uses the slice [b * per_warp, (b + 1) * per_warp) doubles.
+__global__ void __launch_bounds__(32) qp_nullspace_noalloc_kernel(const NullSpaceArgs a, double* __restrict__ scratch,
+                                                                  const long long per_warp) {
+  const int n = a.n, k = a.k;
+  double* work = scratch + (long long)blockIdx.x * per_warp;
+  for (long long p = blockIdx.x; p < a.batch; p += gridDim.x) {
+    __syncwarp();
+    const int st = ns_solve_warp(n, k, a.G + p * (long long)n * n, a.c + p * n, a.A + p * (long long)n * k, a.b + p * k,
+                                 a.x + p * n, work);
+    if (threadIdx.x == 0) a.status[p] = st;
+  }
+}
+}  // namespace mo
+
+namespace {
+double* g_noalloc_ptr[64] = {};  // device address of the scratch array per device, resolved once
+std::mutex g_noalloc_mu;
+}  // namespace
+
+extern "C" int mo_qp_nullspace_solve_batch_noalloc(const mo_qp_batch* problems, double* x, int32_t* status, int device,
+                                                   void* cuda_stream) {
+  MO_TRACE();
+  if (!problems || problems->n <= 0 || problems->k <= 0 || problems->k > problems->n || problems->batch < 0)
+    return MO_ERR_INVALID_ARGUMENT;
+  if (problems->batch == 0) return MO_OK;
+  if (!problems->G || !problems->c || !problems->A_eq || !problems->b_eq || !x || !status) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->flags & kHostOnlyFlags) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->n > MO_NOALLOC_MAX_N) {
+    g_last_error = "mo_qp_nullspace_solve_batch_noalloc: n = " + std::to_string(problems->n) + " exceeds MO_NOALLOC_MAX_N = " +
+                   std::to_string(MO_NOALLOC_MAX_N) + " (static scratch of " + std::to_string(mo::kNoAllocScratchBytes >> 20) +
+                   " MiB); use mo_qp_nullspace_solve_batch";
+    return MO_ERR_UNSUPPORTED_SHAPE;
+  }
+  DeviceInfo dev;
+  int rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);  // the symbol address is per device: resolve it with THIS device current
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  double* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+      void* p = nullptr;
+      MO_CUDA(cudaGetSymbolAddress(&p, mo::g_noalloc_scratch));
+      g_noalloc_ptr[device] = static_cast<double*>(p);
+    }
+    scratch = g_noalloc_ptr[device];
+  }
+  // per-warp slice rounded up to 256 bytes; as many resident warps as the array holds (at least 1 by the n limit)
+  const long long per_warp = (long long)((mo::ns_smem_doubles(problems->n, problems->k) + 31) & ~size_t(31));
+  long long grid = (long long)(mo::kNoAllocScratchBytes / sizeof(double)) / per_warp;
+  const long long cap = (long long)dev.sms * 16;
+  if (grid > cap) grid = cap;
+  if (grid > problems->batch) grid = problems->batch;
+  if (grid < 1) { g_last_error = "mo_qp_nullspace_solve_batch_noalloc: workspace of one problem exceeds the static scratch"; return MO_ERR_UNSUPPORTED_SHAPE; }
+  const mo::NullSpaceArgs a{problems->n, problems->k, problems->batch, problems->G, problems->c, problems->A_eq,
+                            problems->b_eq, x, status};
+  mo::qp_nullspace_noalloc_kernel<<<(int)grid, 32, 0, static_cast<cudaStream_t>(cuda_stream)>>>(a, scratch, per_warp);
+  g_launches.fetch_add(1);
+  MO_CUDA(cudaGetLastError());
+  return MO_OK;
+}
