@@ -182,6 +182,8 @@ enum { MO_QP_NULLSPACE_SUCCESS = 0, MO_QP_NULLSPACE_NOT_POSITIVE_DEFINITE = 1, M
  * constraints and no inequalities (source/nonlinear.cc:83-89); mo_nls_solve_chain_ik_batch does the same.
  */
 int mo_qp_nullspace_solve_batch(const mo_qp_batch* problems, double* x, int32_t* status, int device, void* cuda_stream);
+/* Same with HOST pointers (H2D, solve, D2H; synchronous): the call QPNullSpaceSolver of the C++ mirror makes. */
+int mo_qp_nullspace_solve_batch_host(const mo_qp_batch* problems, double* x, int32_t* status, int device);
 
 /*
  * No counterpart in the reference: added for callers that cannot call cudaMalloc

@@ -34,7 +34,10 @@ enum class StepSizeSelectionResult {                                            
 };
 enum class NLSTerminationState {                                                       // structs.hpp:225-240
   MAX_ITERATIONS, SATISFIED_ABSOLUTE_TOL, SATISFIED_RELATIVE_TOL, SATISFIED_FIRST_ORDER_TOL, MAX_LAMBDA, QP_INDEFINITE,
-  USER_CALLBACK
+  USER_CALLBACK,
+  // batched stand-in (== MO_NLS_QP_FAILED): the inner QP threw FailedFactorization / hit F_ASSERT(s > 0) for THIS problem;
+  // the batch goes on. The batch-of-one Solve() rethrows like the reference.
+  QP_FAILED
 };
 
 struct Errors {  // structs.hpp:169-186
@@ -67,6 +70,7 @@ struct NLSSolverOutputs {  // structs.hpp:293-301
   NLSTerminationState termination_state = NLSTerminationState::MAX_ITERATIONS;
   std::vector<NLSIteration> iterations;
   Vector variables;  // batched API: the final variables travel with the outputs
+  int qp_failure_status = 0;  // QP_FAILED: MO_QP_FAILED_FACTORIZATION or MO_QP_NONPOSITIVE_SLACK of the inner solve
 };
 
 // Type-erased residual (residual.hpp:25-118). `Model<R, P>` wraps a functor
@@ -200,6 +204,10 @@ class ConstrainedNonlinearLeastSquares {
   NLSSolverOutputs Solve(const Params& params, const Vector& variables, int device = 0) {
     std::vector<NLSSolverOutputs> out = SolveBatch({p_}, params, {variables}, custom_retraction_, device);
     variables_ = out[0].variables;
+    if (out[0].termination_state == NLSTerminationState::QP_FAILED) {  // one problem: throw like the reference
+      if (out[0].qp_failure_status == MO_QP_NONPOSITIVE_SLACK) throw std::runtime_error("Some slack variables s <= 0");
+      throw FailedFactorization("Failed to solve self-adjoint system");
+    }
     return std::move(out[0]);
   }
   const Vector& variables() const { return variables_; }
@@ -289,17 +297,47 @@ class ConstrainedNonlinearLeastSquares {
         qps.push_back(st[i].qp);
       }
       if (active.empty()) break;
-      qp_params.initial_guess_method = problems[active[0]]->equality_constraints.empty()
-                                           ? InitialGuessMethod::NAIVE : InitialGuessMethod::SOLVE_EQUALITY_CONSTRAINED;
-      const std::vector<QPInteriorPointSolverOutputs> sol = QPInteriorPointSolver::SolveBatch(qps, qp_params, device);
+      const Problem& first = *problems[active[0]];
+      // Solver choice of the reference (nonlinear.cc:83-89): equality constraints and no inequalities -> QPNullSpaceSolver
+      const bool null_space = first.inequality_constraints.empty() && !first.equality_constraints.empty();
+      qp_params.initial_guess_method = first.equality_constraints.empty() ? InitialGuessMethod::NAIVE
+                                                                          : InitialGuessMethod::SOLVE_EQUALITY_CONSTRAINED;
+      std::vector<QPInteriorPointSolverOutputs> sol;
+      std::vector<int> ns_status;
+      std::vector<Vector> ns_x;
+      if (null_space) ns_status = QPNullSpaceSolver::SolveBatch(qps, &ns_x, device);
+      else sol = QPInteriorPointSolver::SolveBatch(qps, qp_params, device);
       for (std::size_t a = 0; a < active.size(); ++a) {
         const std::size_t i = active[a];
         State& s = st[i];
         const Problem& prob = *problems[i];
-        const QPInteriorPointSolverOutputs& q = sol[a];
-        if (q.batch_status == MO_QP_FAILED_FACTORIZATION) throw FailedFactorization("Failed to solve self-adjoint system");
         const int n = prob.dimension;
-        s.dx.assign(q.variables.begin(), q.variables.begin() + n);
+        QPInteriorPointSolverOutputs q_ns;  // null-space: one "iteration" per solve (NumQPIterations, structs.cc:208-219)
+        q_ns.num_iterations = 1;
+        q_ns.termination_state = QPInteriorPointTerminationState::SATISFIED_KKT_TOL;
+        const QPInteriorPointSolverOutputs& q = null_space ? q_ns : sol[a];
+        if (null_space) {
+          if (ns_status[a] == MO_QP_NULLSPACE_NOT_POSITIVE_DEFINITE) {  // QPWasIndefinite, nonlinear.cc:103-105
+            out[i].termination_state = NLSTerminationState::QP_INDEFINITE;
+            s.done = true;
+            continue;
+          }
+          if (ns_status[a] != MO_QP_NULLSPACE_SUCCESS) {
+            out[i].termination_state = NLSTerminationState::QP_FAILED;
+            s.done = true;
+            continue;
+          }
+          s.dx = ns_x[a];
+        } else {
+          // per-problem numerical trouble never aborts the batch: 2 = FailedFactorization (qp.cc:303-307), 3 = F_ASSERT(s > 0) (:285)
+          if (q.batch_status == MO_QP_FAILED_FACTORIZATION || q.batch_status == MO_QP_NONPOSITIVE_SLACK) {
+            out[i].termination_state = NLSTerminationState::QP_FAILED;
+            out[i].qp_failure_status = q.batch_status;
+            s.done = true;
+            continue;
+          }
+          s.dx.assign(q.variables.begin(), q.variables.begin() + n);
+        }
         // ComputeQPCostDerivative, nonlinear.cc:457-482
         DirectionalDerivatives dd{};
         for (int j = 0; j < n; ++j) dd.d_f += s.qp.c[j] * s.dx[j];
@@ -309,10 +347,25 @@ class ConstrainedNonlinearLeastSquares {
           for (int j = 0; j < n; ++j) dot += s.qp.A_eq(r, j) * s.dx[j];
           dd.d_equality += sign * dot;
         }
-        // SelectPenalty (equation 18.32), nonlinear.cc:112-119, 484-490
-        if (!prob.equality_constraints.empty() && q.lagrange_multipliers) {
-          const double new_penalty = q.lagrange_multipliers->l_infinity;
-          if (new_penalty > s.penalty) s.penalty = new_penalty * params.equality_penalty_scale_factor;
+        // SelectPenalty, nonlinear.cc:112-119, 484-502: |y|_inf from the interior point solve (18.32), or, with the
+        // null-space solver (no multipliers), inequality (18.36)
+        if (!prob.equality_constraints.empty()) {
+          std::optional<double> new_penalty;
+          if (!null_space && q.lagrange_multipliers) {
+            new_penalty = q.lagrange_multipliers->l_infinity;
+          } else if (null_space) {
+            double l1 = 0, cdx = 0, quad = 0;
+            for (int r = 0; r < s.qp.b_eq.rows(); ++r) l1 += std::abs(s.qp.b_eq[r]);
+            l1 = std::max(l1, std::numeric_limits<double>::epsilon());
+            for (int j = 0; j < n; ++j) cdx += s.qp.c[j] * s.dx[j];
+            for (int r = 0; r < n; ++r) {
+              double acc = 0;
+              for (int j = 0; j < n; ++j) acc += (r >= j ? s.qp.G(r, j) : s.qp.G(j, r)) * s.dx[j];  // selfadjointView<Lower>
+              quad += s.dx[r] * acc;
+            }
+            new_penalty = (cdx + 0.5 * std::max(0.0, quad)) / ((1 - params.equality_penalty_rho) * l1);
+          }
+          if (new_penalty && *new_penalty > s.penalty) s.penalty = *new_penalty * params.equality_penalty_scale_factor;
         }
         std::vector<LineSearchStep> steps;
         const StepSizeSelectionResult step = SelectStepSize(prob, params, s.x, s.dx, s.errors_pre, dd, s.penalty, retraction,
@@ -335,11 +388,15 @@ class ConstrainedNonlinearLeastSquares {
 
  private:
   static void CheckParams(const Params& p) {  // nonlinear.cc:49-73
-    const bool ok = p.max_iterations >= 0 && p.max_qp_iterations >= 1 && p.termination_kkt_tolerance > 0 &&
-                    p.absolute_exit_tol > 0 && p.relative_exit_tol >= 0 && p.relative_exit_tol <= 1 &&
-                    p.absolute_first_derivative_tol >= 0 && p.max_line_search_iterations >= 0 &&
-                    p.armijo_search_tau > 0 && p.armijo_search_tau < 1 && p.equality_penalty_initial > 0 &&
-                    p.lambda_initial >= 0 && p.lambda_failure_init > 0 && p.max_lambda > 0 && p.min_lambda >= 0;
+    // the same condition list as check_nls_params of the C ABI (capi.cu), i.e. the reference's F_ASSERTs
+    const bool ok =
+        p.max_iterations >= 0 && p.max_qp_iterations >= 1 && p.termination_kkt_tolerance > 0 && p.absolute_exit_tol > 0 &&
+        p.max_line_search_iterations >= 0 && p.relative_exit_tol >= 0 && p.relative_exit_tol <= 1 &&
+        p.absolute_first_derivative_tol >= 0 && p.armijo_search_tau > 0 && p.armijo_search_tau < 1 &&
+        p.equality_penalty_initial >= 0 && p.equality_penalty_scale_factor >= 1.0 && p.equality_penalty_rho >= 0 &&
+        p.equality_penalty_rho < 1 && p.max_lambda >= 0 && p.min_lambda <= p.max_lambda && p.lambda_initial >= p.min_lambda &&
+        p.lambda_initial <= p.max_lambda && p.lambda_failure_init >= 0 && p.lambda_decrease_on_success >= 0 &&
+        p.lambda_decrease_on_success < 1.0 && p.lambda_decrease_on_restore >= 0 && p.lambda_decrease_on_restore < 1.0;
     if (!ok) throw std::invalid_argument("invalid ConstrainedNonlinearLeastSquares::Params (nonlinear.cc:49-73)");
   }
 

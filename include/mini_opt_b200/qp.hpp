@@ -121,7 +121,9 @@ class QPInteriorPointSolver {
   // One problem = a batch of one (host buffers; H2D, solve, D2H inside). Throws FailedFactorization like qp.cc:303-307.
   QPInteriorPointSolverOutputs Solve(const Params& params, int device = 0) {
     if (!p_) throw std::invalid_argument("Must have a valid problem");
-    std::vector<QPInteriorPointSolverOutputs> out = SolveBatch({*p_}, params, device);
+    std::vector<Vector> init;
+    if (params.initial_guess_method == InitialGuessMethod::USER_PROVIDED) init.push_back(variables_);
+    std::vector<QPInteriorPointSolverOutputs> out = SolveBatch({*p_}, params, device, init.empty() ? nullptr : &init);
     if (out[0].batch_status == MO_QP_FAILED_FACTORIZATION) throw FailedFactorization("Failed to solve self-adjoint system");
     if (out[0].batch_status == MO_QP_NONPOSITIVE_SLACK) throw std::runtime_error("Some slack variables s <= 0");
     variables_ = out[0].variables;
@@ -130,14 +132,34 @@ class QPInteriorPointSolver {
 
   const Vector& variables() const { return variables_; }
   const QP& problem() const { return *p_; }
+  // qp.cc:221: the start point [x | s | y | z] for InitialGuessMethod::USER_PROVIDED (n + 2m + k entries)
+  void SetVariables(const Vector& v) {
+    if (!p_) throw std::invalid_argument("Must have a valid problem");
+    const std::size_t want = p_->G.rows() + 2 * p_->constraints.size() + p_->A_eq.rows();
+    if (v.size() != want) throw std::invalid_argument("SetVariables: wrong size");
+    variables_ = v;
+  }
+  // x_block() / s_block() / y_block() / z_block() of the reference (qp.hpp:187-198) as copies of the slices
+  Vector x_block() const { return Slice(0, p_->G.rows()); }
+  Vector s_block() const { return Slice(p_->G.rows(), static_cast<int>(p_->constraints.size())); }
+  Vector y_block() const { return Slice(p_->G.rows() + static_cast<int>(p_->constraints.size()), p_->A_eq.rows()); }
+  Vector z_block() const {
+    return Slice(p_->G.rows() + static_cast<int>(p_->constraints.size()) + p_->A_eq.rows(), static_cast<int>(p_->constraints.size()));
+  }
 
   // Batched entry point: every problem must have the same (n, k, m). Per-problem failures are reported in
   // `batch_status`, never thrown. `flags_box_pairs`: the constraints of every problem are the interleaved pairs
   // Var(i) >= lo_i, Var(i) <= hi_i for i = 0..n-1 (selects the tuned kernels).
+  // `initial_variables`: one [x | s | y | z] start point per problem, required for InitialGuessMethod::USER_PROVIDED
+  // (the batched SetVariables) and ignored otherwise.
   static std::vector<QPInteriorPointSolverOutputs> SolveBatch(const std::vector<QP>& qps, const Params& params,
-                                                              int device = 0) {
+                                                              int device = 0,
+                                                              const std::vector<Vector>* initial_variables = nullptr) {
     std::vector<QPInteriorPointSolverOutputs> result(qps.size());
     if (qps.empty()) return result;
+    const bool user_guess = params.initial_guess_method == InitialGuessMethod::USER_PROVIDED;
+    if (user_guess && (!initial_variables || initial_variables->size() != qps.size()))
+      throw std::invalid_argument("USER_PROVIDED needs SetVariables / one initial [x|s|y|z] per problem");
     const int n = qps[0].G.rows(), k = qps[0].A_eq.rows(), m = static_cast<int>(qps[0].constraints.size());
     const std::int64_t B = static_cast<std::int64_t>(qps.size()), stride = mo_qp_vars_stride(n, k, m);
     std::vector<double> G(B * n * n), c(B * n), A(B * k * n + 1), b(B * k + 1), ia(B * m + 1), ib(B * m + 1);
@@ -149,6 +171,11 @@ class QPInteriorPointSolver {
       Check(q);
       if (q.G.rows() != n || q.A_eq.rows() != k || static_cast<int>(q.constraints.size()) != m)
         throw std::invalid_argument("SolveBatch needs problems of identical shape");
+      if (user_guess) {
+        const Vector& v0 = (*initial_variables)[p];
+        if (static_cast<std::int64_t>(v0.size()) != stride) throw std::invalid_argument("initial variables: wrong size");
+        for (std::int64_t i = 0; i < stride; ++i) vars[p * stride + i] = v0[i];
+      }
       for (int i = 0; i < n * n; ++i) G[p * n * n + i] = q.G.data()[i];
       for (int i = 0; i < n; ++i) c[p * n + i] = q.c[i];
       for (int i = 0; i < k * n; ++i) A[p * k * n + i] = q.A_eq.data()[i];
@@ -197,8 +224,60 @@ class QPInteriorPointSolver {
     for (const LinearInequalityConstraint& con : q.constraints)
       if (con.variable < 0 || con.variable >= q.G.rows()) throw std::invalid_argument("constraint index out of bounds");
   }
+  Vector Slice(int begin, int count) const {
+    if (static_cast<int>(variables_.size()) < begin + count) return Vector(static_cast<std::size_t>(count), 0.0);
+    return Vector(variables_.begin() + begin, variables_.begin() + begin + count);
+  }
   const QP* p_ = nullptr;
   Vector variables_;
+};
+
+enum class QPNullSpaceTerminationState { SUCCESS = 0, NOT_POSITIVE_DEFINITE = 1 };  // structs.hpp:137-142
+
+// qp.hpp:304-319: equality-constrained QP by the null-space method (source/qp.cc:679-729); the inequality constraints of
+// the problem are ignored like in the reference. SolveBatch: problems of identical (n, k), one device call.
+class QPNullSpaceSolver {
+ public:
+  QPNullSpaceTerminationState Solve(const QP& p, int device = 0) {
+    std::vector<Vector> x;
+    const std::vector<int> st = SolveBatch({p}, &x, device);
+    if (st[0] == MO_QP_NULLSPACE_RANK_DEFICIENT) throw std::runtime_error("A_eq is rank deficient");
+    x_ = x[0];
+    return static_cast<QPNullSpaceTerminationState>(st[0]);
+  }
+  const Vector& variables() const { return x_; }
+
+  // Returns MO_QP_NULLSPACE_* per problem; x[i] = 0 unless SUCCESS.
+  static std::vector<int> SolveBatch(const std::vector<QP>& qps, std::vector<Vector>* x, int device = 0) {
+    std::vector<int> result(qps.size(), 0);
+    x->assign(qps.size(), Vector());
+    if (qps.empty()) return result;
+    const int n = qps[0].G.rows(), k = qps[0].A_eq.rows();
+    if (k <= 0) throw std::invalid_argument("Problem must have at least one equality constraint");
+    const std::int64_t B = static_cast<std::int64_t>(qps.size());
+    std::vector<double> G(B * n * n), c(B * n), A(B * k * n), b(B * k), xs(B * n);
+    std::vector<std::int32_t> status(B);
+    for (std::int64_t p = 0; p < B; ++p) {
+      const QP& q = qps[p];
+      if (q.G.rows() != n || q.G.cols() != n || q.c.rows() != n || q.A_eq.rows() != k || q.A_eq.cols() != n || q.b_eq.rows() != k)
+        throw std::invalid_argument("QPNullSpaceSolver::SolveBatch needs problems of identical shape");
+      for (int i = 0; i < n * n; ++i) G[p * n * n + i] = q.G.data()[i];
+      for (int i = 0; i < n; ++i) c[p * n + i] = q.c[i];
+      for (int i = 0; i < k * n; ++i) A[p * k * n + i] = q.A_eq.data()[i];
+      for (int i = 0; i < k; ++i) b[p * k + i] = q.b_eq[i];
+    }
+    mo_qp_batch batch{n, k, 0, 0, B, G.data(), c.data(), A.data(), b.data(), nullptr, nullptr, nullptr, nullptr};
+    const int rc = mo_qp_nullspace_solve_batch_host(&batch, xs.data(), status.data(), device);
+    if (rc != MO_OK) throw std::runtime_error(std::string("mini_opt_b200 error ") + std::to_string(rc) + ": " + mo_last_error_string());
+    for (std::int64_t p = 0; p < B; ++p) {
+      result[p] = status[p];
+      (*x)[p].assign(xs.begin() + p * n, xs.begin() + (p + 1) * n);
+    }
+    return result;
+  }
+
+ private:
+  Vector x_;
 };
 
 }  // namespace mini_opt_b200

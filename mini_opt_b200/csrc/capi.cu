@@ -897,6 +897,40 @@ extern "C" int mo_debug_read_trace(long long* out, int cap) {
 }
 #endif
 
+// Host-pointer variant of mo_qp_nullspace_solve_batch (the call the C++ mirror's QPNullSpaceSolver makes): H2D, solve, D2H,
+// synchronous. Plain cudaMalloc / cudaFree per call: equality-only QPs are the small side path of the NLS driver.
+extern "C" int mo_qp_nullspace_solve_batch_host(const mo_qp_batch* problems, double* x, int32_t* status, int device) {
+  MO_TRACE();
+  if (!problems || problems->n <= 0 || problems->k <= 0 || problems->batch < 0) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->batch == 0) return MO_OK;
+  if (!problems->G || !problems->c || !problems->A_eq || !problems->b_eq || !x || !status) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->flags & kHostOnlyFlags) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  int rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  const size_t n = problems->n, k = problems->k, B = (size_t)problems->batch, d = sizeof(double);
+  const size_t oG = 0, oc = align256(oG + B * n * n * d), oA = align256(oc + B * n * d), ob = align256(oA + B * n * k * d),
+               ox = align256(ob + B * k * d), os = align256(ox + B * n * d), total = align256(os + B * sizeof(int32_t));
+  char* D = nullptr;
+  MO_CUDA(cudaMalloc(&D, total));
+  auto fail = [&](cudaError_t e, const char* what) { cudaFree(D); return cuda_fail(e, what); };
+  cudaError_t e;
+  if ((e = cudaMemcpy(D + oG, problems->G, B * n * n * d, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e, "H2D G");
+  if ((e = cudaMemcpy(D + oc, problems->c, B * n * d, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e, "H2D c");
+  if ((e = cudaMemcpy(D + oA, problems->A_eq, B * n * k * d, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e, "H2D A_eq");
+  if ((e = cudaMemcpy(D + ob, problems->b_eq, B * k * d, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e, "H2D b_eq");
+  mo_qp_batch db = *problems;
+  db.G = (const double*)(D + oG); db.c = (const double*)(D + oc); db.A_eq = (const double*)(D + oA); db.b_eq = (const double*)(D + ob);
+  rc = mo_qp_nullspace_solve_batch(&db, (double*)(D + ox), (int32_t*)(D + os), device, nullptr);
+  if (rc) { cudaFree(D); return rc; }
+  if ((e = cudaMemcpy(x, D + ox, B * n * d, cudaMemcpyDeviceToHost)) != cudaSuccess) return fail(e, "D2H x");
+  if ((e = cudaMemcpy(status, D + os, B * sizeof(int32_t), cudaMemcpyDeviceToHost)) != cudaSuccess) return fail(e, "D2H status");
+  MO_CUDA(cudaFree(D));
+  return MO_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // No-allocation entry point (no counterpart in the reference).
 // Variant of qp_nullspace_kernel whose per-warp workspace (QR, Q, G Z, Z'G Z, vectors: ns_smem_doubles(n, k) doubles)

@@ -8,6 +8,7 @@
 // include/mini_opt_b200/nonlinear.hpp's SolveBatch on the same problems.
 #include <cmath>
 #include <cstdio>
+#include <random>
 #include <vector>
 
 #include "mini_opt/nonlinear.hpp"
@@ -64,6 +65,43 @@ int main() {
     p.max_qp_iterations = 10;
     Run("rosenbrock_ineq", problem, p,
         {{12, -5}, {100.0, -20.0}, {1423.0, -400.0}, {-20.0, 10.0}, {-120.0, 35.0}, {-50.0, 0.5}});
+  }
+  {
+    // TestSphereWithNonlinearEqualityConstraints (nonlinear_test.cc:745-830): n = 6, two nonlinear equalities, no
+    // inequalities -> QPNullSpaceSolver + the (18.36) penalty. 100 seeded start points (std::mt19937{7}, as in
+    // tests/cpp/test_nls_host_api.cc); x0, x1 of the result are printed.
+    constexpr int N = 6;
+    Problem problem{};
+    problem.costs.push_back(MakeResidual<N, N>({0, 1, 2, 3, 4, 5}, [](const Eigen::Matrix<double, N, 1>& x, Eigen::Matrix<double, N, N>* J) {
+      if (J) J->setIdentity();
+      return Eigen::Matrix<double, N, 1>(x);
+    }));
+    problem.dimension = N;
+    auto product = [](double v) {
+      return [v](const Vector2d& x, Eigen::Matrix<double, 1, 2>* J) -> Eigen::Matrix<double, 1, 1> {
+        if (J) { (*J)(0, 0) = x[1]; (*J)(0, 1) = x[0]; }
+        return Eigen::Matrix<double, 1, 1>{x[0] * x[1] - v};
+      };
+    };
+    problem.equality_constraints.push_back(MakeResidual<1, 2>({0, 1}, product(4.0)));
+    problem.equality_constraints.push_back(MakeResidual<1, 2>({2, 3}, product(9.0)));
+    ConstrainedNonlinearLeastSquares::Params p{};
+    p.max_iterations = 100;
+    p.max_qp_iterations = 1;
+    p.relative_exit_tol = 1e-12;
+    p.absolute_first_derivative_tol = 1e-9;
+    p.termination_kkt_tolerance = 1e-6;
+    p.lambda_initial = 0.001;
+    std::mt19937 engine{7};
+    std::uniform_real_distribution<double> dist{-30.0, 30.0};
+    ConstrainedNonlinearLeastSquares nls(&problem);
+    for (int i = 0; i < 100; ++i) {
+      Eigen::VectorXd g(N);
+      for (int j = 0; j < N; ++j) g[j] = dist(engine);
+      const NLSSolverOutputs out = nls.Solve(p, g);
+      std::printf("sphere %d %d %zu %d %.17g %.17g\n", i, static_cast<int>(out.termination_state), out.iterations.size(),
+                  static_cast<int>(out.NumQPIterations()), nls.variables()[0], nls.variables()[1]);
+    }
   }
   return 0;
 }

@@ -53,6 +53,43 @@ int main(int argc, char** argv) {
   }
   const auto res = QPInteriorPointSolver::SolveBatch(batch, params);
   for (const auto& o : res) CHECK(o.batch_status == 0 && std::fabs(o.x(0) - 4.0) < 1e-6 && std::fabs(o.x(1) + 1.0) < 1e-6);
+  // USER_PROVIDED through SetVariables (qp.cc:221): start at the solved point -> converges again, in few iterations
+  {
+    QPInteriorPointSolver::Params up = params;
+    up.initial_guess_method = InitialGuessMethod::USER_PROVIDED;
+    QPInteriorPointSolver cold(&qp);
+    threw = false;
+    try { (void)cold.Solve(up); } catch (const std::invalid_argument&) { threw = true; }  // no SetVariables yet
+    CHECK(threw);
+    Vector start = {3.0, 1.0, 1.0};  // [x | s | z]: interior point
+    cold.SetVariables(start);
+    const QPInteriorPointSolverOutputs warm = cold.Solve(up);
+    CHECK(warm.termination_state == QPInteriorPointTerminationState::SATISFIED_KKT_TOL && std::fabs(warm.x(0) - 4.0) < 1e-6);
+    CHECK(cold.x_block().size() == 1 && cold.s_block().size() == 1 && cold.y_block().empty() && cold.z_block().size() == 1);
+    CHECK(std::fabs(cold.x_block()[0] - 4.0) < 1e-6 && std::fabs(cold.z_block()[0] - 2.0) < 1e-5);
+    threw = false;
+    try { cold.SetVariables(Vector{1.0}); } catch (const std::invalid_argument&) { threw = true; }
+    CHECK(threw);
+  }
+  // QPNullSpaceSolver: TestNullSpaceSolver1 (test/qp_test.cc:576-626): |A x - b|^2 with x1 pinned to 0.3
+  {
+    QP ns(2);
+    const double A[2][2] = {{-2.0, 1.4}, {2.2, -3.5}}, b[2] = {-0.8, 1.3};
+    for (int i = 0; i < 2; ++i)
+      for (int j = 0; j < 2; ++j) {
+        ns.G(i, j) = A[0][i] * A[0][j] + A[1][i] * A[1][j];  // UpdateHessian: J'J
+      }
+    for (int i = 0; i < 2; ++i) ns.c[i] = -(A[0][i] * b[0] + A[1][i] * b[1]);  // J'r at x = 0
+    ns.A_eq.resize(1, 2);
+    ns.A_eq(0, 1) = 1.0;
+    ns.b_eq = Vector{-0.3};
+    QPNullSpaceSolver nss;
+    CHECK(nss.Solve(ns) == QPNullSpaceTerminationState::SUCCESS);
+    CHECK(std::fabs(nss.variables()[1] - 0.3) < 1e-12 && std::fabs(nss.variables()[0] - 0.860859728506787) < 1e-12);
+    QP flat = ns;
+    flat.G = Matrix(2, 2);  // reduced Hessian 0 -> NOT_POSITIVE_DEFINITE
+    CHECK(nss.Solve(flat) == QPNullSpaceTerminationState::NOT_POSITIVE_DEFINITE);
+  }
   std::printf("gpu ok\n");
   return 0;
 }

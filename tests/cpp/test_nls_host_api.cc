@@ -150,6 +150,7 @@ static void TestSphereWithNonlinearEqualityConstraints() {  // nonlinear_test.cc
   }
   const std::vector<const Problem*> problems(guesses.size(), &problem);
   const std::vector<NLSSolverOutputs> out = ConstrainedNonlinearLeastSquares::SolveBatch(problems, p, guesses);
+  PrintResults("sphere", out);
   int good = 0;
   for (const NLSSolverOutputs& o : out) {
     CHECK(SatisfiedTol(o.termination_state));
@@ -162,6 +163,49 @@ static void TestSphereWithNonlinearEqualityConstraints() {  // nonlinear_test.cc
   CHECK(good == static_cast<int>(out.size()));
 }
 
+// A singular problem inside a batch ends as QP_FAILED for itself; the others go on. The batch-of-one
+// Solve() throws FailedFactorization like the reference (qp.cc:303-307). CheckParams follows nonlinear.cc:49-73.
+static void TestPerProblemFailureAndParams() {
+  Problem good;
+  good.dimension = 2;
+  good.costs.push_back(MakeResidual<2, 2>({0, 1}, &Rosenbrock));
+  good.inequality_constraints.push_back(Var(0) >= -50.0);
+  Problem singular;  // J = 0 and lambda = 0: G = 0 -> zero pivots in the KKT factorization
+  singular.dimension = 2;
+  singular.costs.push_back(MakeResidual<2, 2>({0, 1}, [](const std::array<double, 2>&, std::array<double, 4>* J) {
+    if (J) J->fill(0.0);
+    return std::array<double, 2>{1.0, 1.0};
+  }));
+  singular.inequality_constraints.push_back(Var(0) >= -50.0);
+  ConstrainedNonlinearLeastSquares::Params p;
+  p.max_iterations = 20;
+  p.max_qp_iterations = 10;
+  const std::vector<NLSSolverOutputs> out =
+      ConstrainedNonlinearLeastSquares::SolveBatch({&good, &singular, &good}, p, {Vector{0.8, -0.3}, Vector{0.0, 0.0}, Vector{4.0, 0.0}});
+  CHECK(out[1].termination_state == NLSTerminationState::QP_FAILED && out[1].qp_failure_status == MO_QP_FAILED_FACTORIZATION);
+  CHECK(SatisfiedTol(out[0].termination_state) && SatisfiedTol(out[2].termination_state));
+  CHECK(std::abs(out[0].variables[0] - 1.0) < 1e-5 && std::abs(out[2].variables[1] - 1.0) < 1e-5);
+  ConstrainedNonlinearLeastSquares one(&singular);
+  bool threw = false;
+  try { (void)one.Solve(p, Vector{0.0, 0.0}); } catch (const FailedFactorization&) { threw = true; }
+  CHECK(threw);
+  // values the reference accepts (>= 0) and values it asserts against
+  ConstrainedNonlinearLeastSquares nls(&good);
+  ConstrainedNonlinearLeastSquares::Params q = p;
+  q.equality_penalty_initial = 0.0; q.lambda_failure_init = 0.0;
+  (void)nls.Solve(q, Vector{0.8, -0.3});
+  for (int bad = 0; bad < 4; ++bad) {
+    q = p;
+    if (bad == 0) { q.min_lambda = 2.0; q.max_lambda = 1.0; }
+    if (bad == 1) q.lambda_decrease_on_success = 1.0;
+    if (bad == 2) q.equality_penalty_scale_factor = 0.5;
+    if (bad == 3) q.equality_penalty_rho = 1.0;
+    threw = false;
+    try { (void)nls.Solve(q, Vector{0.8, -0.3}); } catch (const std::invalid_argument&) { threw = true; }
+    CHECK(threw);
+  }
+}
+
 int main(int argc, char** argv) {
   const std::string mode = argc > 1 ? argv[1] : "cpu";
   TestLinearization();
@@ -170,6 +214,7 @@ int main(int argc, char** argv) {
   TestRosenbrock(true);
   TestInequalityConstrainedRosenbrock();
   TestSphereWithNonlinearEqualityConstraints();
+  TestPerProblemFailureAndParams();
   std::printf("gpu ok\n");
   return 0;
 }
