@@ -217,11 +217,10 @@ int launch_dm(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
   return MO_OK;
 }
 
-// MO_QP_DM_KERNEL=cta selects the CTA-per-problem kernel (qp_dmma.cuh) for A/B runs; default: warp per problem.
-bool dm_use_cta_kernel() {
-  const char* e = getenv("MO_QP_DM_KERNEL");
-  return e && e[0] == 'c';
-}
+// mo_debug_set_dm_kernel(1) selects the CTA-per-problem kernel (qp_dmma.cuh), the cross-check partner of the default
+// warp-per-problem kernel, for the variant-agreement test and A/B measurements. No environment variables are read.
+std::atomic<int> g_dm_kernel{0};
+bool dm_use_cta_kernel() { return g_dm_kernel.load() == 1; }
 
 bool dm_eligible(int n, int k, int m, int flags, bool ragged, int strategy) {
   if (!(flags & MO_QP_FLAG_BOX_PAIRS) || ragged || m != 2 * n) return false;
@@ -359,6 +358,8 @@ int64_t mo_qp_vars_stride(int32_t n, int32_t k, int32_t m) { return (int64_t)n +
 int mo_abi_version(void) { return MO_ABI_VERSION; }
 
 int mo_debug_set_tma(int enabled) { return g_w16_tma.exchange(enabled ? 1 : 0); }
+
+int mo_debug_set_dm_kernel(int which) { return g_dm_kernel.exchange(which == 1 ? 1 : 0); }
 
 int64_t mo_kernel_launch_count(void) { return g_launches.load(); }
 

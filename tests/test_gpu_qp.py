@@ -302,18 +302,18 @@ def test_full_size_properties(dev):
     assert torch.equal(out2.vars, out.vars[:50000][perm]) and torch.equal(out2.iters, out.iters[:50000][perm])
 
 
-# The three DMMA kernels behind the same shapes: warp per problem (default), its two-warp look-ahead variant, and the
-# CTA-per-problem kernel; selected per call through the environment (read at dispatch time).
-DMMA_VARIANTS = {"warp": {"MO_QP_WD_WARPS": "1"}, "warp2": {"MO_QP_WD_WARPS": "2"}, "cta": {"MO_QP_DM_KERNEL": "cta"}}
+# The two DMMA kernels behind the same shapes: warp per problem (default) and the CTA-per-problem kernel, selected
+# through the explicit debug hook of the ABI (mo_debug_set_dm_kernel; the library reads no environment variables).
+DMMA_VARIANTS = {"warp": 0, "cta": 1}
 
 
 @pytest.fixture
-def dmma_variant(request, monkeypatch):
-    monkeypatch.delenv("MO_QP_WD_WARPS", raising=False)
-    monkeypatch.delenv("MO_QP_DM_KERNEL", raising=False)
-    for key, val in DMMA_VARIANTS[request.param].items():
-        monkeypatch.setenv(key, val)
-    return request.param
+def dmma_variant(request):
+    from mini_opt_b200 import lib
+    L = lib.load()
+    L.mo_debug_set_dm_kernel(DMMA_VARIANTS[request.param])
+    yield request.param
+    L.mo_debug_set_dm_kernel(0)
 
 
 @pytest.mark.gpu
@@ -366,8 +366,8 @@ def test_dmma_shapes_properties_and_determinism(dev, n, k, B, dmma_variant):
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,k,B", [(64, 16, 2048), (32, 8, 4096), (16, 8, 4096)])
 @pytest.mark.parametrize("guess", [abi.MO_GUESS_NAIVE, abi.MO_GUESS_SOLVE_EQUALITY_CONSTRAINED])
-def test_dmma_kernel_variants_agree(dev, monkeypatch, n, k, B, guess):
-    """The warp-per-problem kernel (1 and 2 warps) and the CTA-per-problem kernel factor the same KKT matrices in a
+def test_dmma_kernel_variants_agree(dev, n, k, B, guess):
+    """The warp-per-problem kernel and the CTA-per-problem kernel factor the same KKT matrices in a
     different order of operations (left-looking from shared-memory tiles vs right-looking in accumulator fragments):
     same status and iteration count on >= 97 % of the problems (start points clamped onto a bound are
     rounding-chaotic; NAIVE starts must agree on all), and x to relative 1e-9 where they do."""
@@ -377,16 +377,15 @@ def test_dmma_kernel_variants_agree(dev, monkeypatch, n, k, B, guess):
     arrs = synth.box_qp_batch_torch(n, k, B, seed=5, device=dev)
     prm = synth.solve_params(guess=guess)
     res = {}
-    for name, env in DMMA_VARIANTS.items():
-        monkeypatch.delenv("MO_QP_WD_WARPS", raising=False)
-        monkeypatch.delenv("MO_QP_DM_KERNEL", raising=False)
-        for key, val in env.items():
-            monkeypatch.setenv(key, val)
+    from mini_opt_b200 import lib
+    for name, which in DMMA_VARIANTS.items():
+        lib.load().mo_debug_set_dm_kernel(which)
         out = qp.alloc_out_torch(B, n, k, m, dev)
         qp.solve_batch_device(arrs, prm, out, dev)
         torch.cuda.synchronize()
         res[name] = qp.out_to_numpy(out)
-    for name, ref_name in (("warp", "cta"), ("warp2", "cta"), ("warp2", "warp")):
+    lib.load().mo_debug_set_dm_kernel(0)
+    for name, ref_name in (("warp", "cta"),):
         got, ref = res[name], res[ref_name]
         same = (got.iters == ref.iters) & (got.status == ref.status)
         assert same.mean() >= (1.0 if guess == abi.MO_GUESS_NAIVE else 0.97), (name, same.mean())
