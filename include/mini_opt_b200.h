@@ -375,6 +375,9 @@ int mo_debug_set_tma(int enabled);
 /* Measurement / cross-check hook: 0 = default kernel for the DMMA shapes (warp per problem, "dmma_warp"), 1 = the
  * CTA-per-problem kernel ("dmma_cta"). Returns the previous value. Process-wide; the library reads no environment. */
 int mo_debug_set_dm_kernel(int which);
+/* Measurement hook: warps per CTA of the lock-step chain-IK kernel (1, 2, 4, 8, 16; -1 on anything else). Results are
+ * bit-identical for every value. Returns the previous value. */
+int mo_debug_set_ik_warps(int warps);
 
 #ifdef __cplusplus
 } /* extern "C" */

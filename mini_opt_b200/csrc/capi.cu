@@ -676,8 +676,8 @@ int mo_qp_ip_solve_batch_host_multi(const mo_qp_batch* problems, const mo_qp_par
 // ---------------------------------------------------------------------------------------------
 // nonlinear least squares entry points
 // ---------------------------------------------------------------------------------------------
-#include "nls_chain.cuh"
-#include "nls_linearize_dmma.cuh"
+#include "nls_launch.h"
+#include "qp_nullspace.cuh"
 
 namespace {
 
@@ -711,15 +711,6 @@ int check_chain(const mo_chain_ik_batch* b, bool fk_only) {
       (b->m > 0 && (!b->ineq_var || !b->ineq_a || !b->ineq_b)) || !b->x0)
     return MO_ERR_INVALID_ARGUMENT;
   return MO_OK;
-}
-
-mo::ChainArgs make_chain_args(const mo_chain_ik_batch* b) {
-  mo::ChainArgs a{};
-  a.links = b->links; a.n = b->n; a.n_cost = b->n_cost; a.cost_block = b->cost_block; a.n_eq = b->n_eq; a.m = b->m;
-  a.batch = b->batch; a.link_pose = b->link_pose; a.link_mask = b->link_mask; a.cost_w = b->cost_w;
-  a.cost_target = b->cost_target; a.eq_w = b->eq_w; a.eq_target = b->eq_target; a.ineq_var = b->ineq_var;
-  a.ineq_a = b->ineq_a; a.ineq_b = b->ineq_b; a.x0 = b->x0;
-  return a;
 }
 
 template <typename K>
@@ -788,36 +779,10 @@ int mo_nls_linearize_batch(const mo_nls_linearize_args* g, int device, void* cud
   if (rc) return rc;
   DeviceGuard guard(device);
   if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
-  mo::LinearizeArgs a{g->n, g->r_cost, g->cost_block, g->r_eq, g->m, g->batch, g->x, g->J_cost, g->r_cost_v, g->J_eq,
-                      g->r_eq_v, g->lambda, g->ineq_var, g->ineq_a, g->ineq_b, g->G, g->c, g->A_eq, g->b_eq,
-                      g->ineq_b_shifted, g->errors};
-  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-  // n = 32 .. 64 (multiple of 8), even row count, 16-byte aligned J / r: the DMMA kernel (nls_linearize_dmma.cuh)
-  auto aligned16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15u) == 0; };
-  if (g->n % 8 == 0 && g->n >= 32 && g->n <= 64 && g->r_cost >= 8 && g->r_cost % 2 == 0 && aligned16(g->J_cost) &&
-      aligned16(g->r_cost_v)) {
-    auto launch = [&](auto kernel) -> int {
-      int bps = 0;
-      MO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32, 0));
-      const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
-      kernel<<<(int)(g->batch < cap ? g->batch : cap), 32, 0, stream>>>(a);
-      g_launches.fetch_add(1);
-      MO_CUDA(cudaGetLastError());
-      return MO_OK;
-    };
-    switch (g->n / 8) {
-      case 4: return launch(mo::nls_linearize_dmma_kernel<4>);
-      case 5: return launch(mo::nls_linearize_dmma_kernel<5>);
-      case 6: return launch(mo::nls_linearize_dmma_kernel<6>);
-      case 7: return launch(mo::nls_linearize_dmma_kernel<7>);
-      default: return launch(mo::nls_linearize_dmma_kernel<8>);
-    }
-  }
-  const long long cap = (long long)dev.sms * 32;
-  mo::nls_linearize_kernel<<<(int)(g->batch < cap ? g->batch : cap), 32, 0, stream>>>(a);
-  g_launches.fetch_add(1);
-  MO_CUDA(cudaGetLastError());
-  return MO_OK;
+  const mo::NlsLaunchInfo info{dev.sms, (size_t)dev.max_smem_optin};
+  rc = mo::nls_launch_linearize(g, info, static_cast<cudaStream_t>(cuda_stream), &g_last_error);
+  if (rc == MO_OK) g_launches.fetch_add(1);
+  return rc;
 }
 
 int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, double* translation, double* rotation_q,
@@ -832,16 +797,11 @@ int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, doub
   if (rc) return rc;
   DeviceGuard guard(device);
   if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
-  const size_t smem = sizeof(double) * mo::chain_smem_doubles(chain->links, chain->n);
-  int grid = 0;
-  rc = warp_grid(mo::chain_fk_kernel, smem, chain->batch, dev, &grid);
-  if (rc) return rc;
-  mo::chain_fk_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(chain), params,
-                                                                                  translation, rotation_q, t_D_params,
-                                                                                  r_D_params);
-  g_launches.fetch_add(1);
-  MO_CUDA(cudaGetLastError());
-  return MO_OK;
+  const mo::NlsLaunchInfo info{dev.sms, (size_t)dev.max_smem_optin};
+  rc = mo::nls_launch_chain_fk(chain, params, translation, rotation_q, t_D_params, r_D_params, info,
+                               static_cast<cudaStream_t>(cuda_stream), &g_last_error);
+  if (rc == MO_OK) g_launches.fetch_add(1);
+  return rc;
 }
 
 int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
@@ -859,29 +819,10 @@ int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_
   if (rc) return rc;
   DeviceGuard guard(device);
   if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
-  const size_t smem = sizeof(double) * mo::nls_smem_doubles(problems->links, problems->n, problems->n_cost,
-                                                            problems->n_eq, problems->m);
-  int grid = 0;
-  rc = warp_grid(mo::nls_chain_ik_kernel, smem, problems->batch, dev, &grid);
-  if (rc) return rc;
-  const mo::NlsParams p{params->max_iterations, params->max_qp_iterations, params->termination_kkt_tolerance,
-                        params->absolute_exit_tol, params->relative_exit_tol, params->absolute_first_derivative_tol,
-                        params->max_line_search_iterations, params->line_search_strategy, params->armijo_search_tau,
-                        params->equality_penalty_initial, params->equality_penalty_scale_factor,
-                        params->equality_penalty_rho, params->lambda_initial, params->lambda_failure_init,
-                        params->lambda_decrease_on_success, params->lambda_decrease_on_restore, params->max_lambda,
-                        params->min_lambda, params->retraction, params->inner_qp_solver};
-  const mo::NlsOut o{out->x, out->termination, out->iterations, out->qp_iterations, out->ls_steps, out->errors};
-  // ticket counter of this launch: a slot of a small ring in device memory, zeroed on the launch stream
-  static std::atomic<unsigned> ring{0};
-  unsigned long long* tickets = nullptr;
-  MO_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&tickets), mo::g_ik_tickets));
-  tickets += ring.fetch_add(1) % mo::kIkTicketSlots;
-  MO_CUDA(cudaMemsetAsync(tickets, 0, sizeof(unsigned long long), static_cast<cudaStream_t>(cuda_stream)));
-  mo::nls_chain_ik_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(cuda_stream)>>>(make_chain_args(problems), p, o, tickets);
-  g_launches.fetch_add(1);
-  MO_CUDA(cudaGetLastError());
-  return MO_OK;
+  const mo::NlsLaunchInfo info{dev.sms, (size_t)dev.max_smem_optin};
+  rc = mo::nls_launch_chain_ik(problems, params, out, info, static_cast<cudaStream_t>(cuda_stream), &g_last_error);
+  if (rc == MO_OK) g_launches.fetch_add(1);
+  return rc;
 }
 
 }  // extern "C"

@@ -10,14 +10,13 @@
 // two sequential scans (suffix poses, prefix rotations), lane i then forms link i's Jacobian columns.
 #pragma once
 
+#include "nls_launch.h"
 #include "qp_generic.cuh"
 #include "qp_warp.cuh"
 #include "qp_nullspace.cuh"
 
 namespace mo {
 
-constexpr int kMaxChainLinks = 32;
-constexpr int kMaxChainRows = 8;  // cost / equality rows per problem
 
 struct ChainArgs {
   int links, n, n_cost, cost_block, n_eq, m;
@@ -121,7 +120,7 @@ __device__ inline double* chain_carve(ChainWork& C, double* q, int links, int n)
 
 // Chain description into shared memory; Euler decomposition of the links with an active rotation.
 __device__ inline void chain_setup(ChainWork& C, const ChainArgs& a) {
-  const int lane = threadIdx.x;
+  const int lane = threadIdx.x & 31;
   for (int e = lane; e < C.links * 7; e += 32) C.pose[e] = a.link_pose[e];
   for (int e = lane; e < C.links * 6; e += 32) C.mask[e] = a.link_mask[e];
   __syncwarp();
@@ -148,7 +147,7 @@ __device__ inline void chain_setup(ChainWork& C, const ChainArgs& a) {
 // ActuatorChain::Update (transform_chains.cc:165-244) with ComputeChain (:23-82), executed by one warp.
 // Returns without work when no parameter moved by more than 1e-9 since the last update (the reference's cache).
 __device__ inline void chain_update(ChainWork& C, const double* params) {
-  const int lane = threadIdx.x, L = C.links, n = C.n;
+  const int lane = threadIdx.x & 31, L = C.links, n = C.n;
   bool changed = false;
   for (int i = lane; i < n; i += 32) changed = changed || fabs(C.cached[i] - params[i]) > 1.0e-9;
   const bool had = *C.have_cache != 0;
@@ -278,7 +277,7 @@ __global__ void __launch_bounds__(32) chain_fk_kernel(const ChainArgs a, const d
   ChainWork C;
   chain_carve(C, smem, a.links, a.n);
   chain_setup(C, a);
-  const int lane = threadIdx.x, n = a.n;
+  const int lane = threadIdx.x & 31, n = a.n;
   for (long long p = blockIdx.x; p < a.batch; p += gridDim.x) {
     if (lane == 0) *C.have_cache = 0;
     __syncwarp();
@@ -303,7 +302,7 @@ __device__ inline void linearize_warp(int n, int r_cost, int cost_block, int k, 
                                       const double* rc, const double* Je, const double* re, double lambda,
                                       const int* ivar, const double* ia, const double* ib, double* G, double* c,
                                       double* A, double* b, double* ib_shift, double* errors) {
-  const int lane = threadIdx.x;
+  const int lane = threadIdx.x & 31;
   const int cb = cost_block > 0 ? cost_block : r_cost;
   for (int e = lane; e < n * n; e += 32) {
     const int col = e / n, row = e - col * n;
@@ -379,7 +378,7 @@ __device__ __forceinline__ double mod_pi(double angle) {  // angle_utils.hpp:9-1
 __device__ inline void chain_rows(ChainWork& C, const double* x, int rows, const double* w, const double* target,
                                   double* r, double* J) {
   chain_update(C, x);
-  const int lane = threadIdx.x, n = C.n;
+  const int lane = threadIdx.x & 31, n = C.n;
   for (int i = lane; i < rows; i += 32)
     r[i] = (w[3 * i] * C.suft[0] + w[3 * i + 1] * C.suft[1]) + w[3 * i + 2] * C.suft[2] - target[i];
   if (J)
@@ -421,33 +420,33 @@ __host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost,
   return d;
 }
 
-// ConstrainedNonlinearLeastSquares::Solve (nonlinear.cc:75-158), one warp (= one 32-thread block) per problem.
-#ifndef MO_IK_MINB
-// resident warps per SM; measured on B200 with the ticket queue, 100K problems (6 links / 12 links, problems/s):
-// 12 -> 700K / 229K, 16 -> 787K / 229K, 24 -> 802K / 203K (80 registers: spills at n = 12), 32 -> 794K / 179K
-#define MO_IK_MINB 16
-#endif
+// ConstrainedNonlinearLeastSquares::Solve (nonlinear.cc:75-158), one warp per problem. Resident warps per SM, measured on
+// B200 in round 1 with one warp per CTA (100K problems, 6 links / 12 links, problems/s): 12 -> 700K / 229K, 16 -> 787K / 229K,
+// 24 -> 802K / 203K (80 registers: spills at n = 12), 32 -> 794K / 179K: the launch bounds below keep W x MINB = 16.
+// Problems are handed out through a global ticket counter (zeroed on the launch stream): SQP iteration counts are heavy-tailed
+// (a few % of the IK problems run to max_iterations), a static stride leaves most warps idle while the unlucky ones finish.
 constexpr int kIkTicketSlots = 64;  // launches in flight that may hold a ticket counter at the same time
 __device__ unsigned long long g_ik_tickets[kIkTicketSlots];
 
-// Next problem of a persistent warp: the first gridDim.x problems are taken by block index, the rest from a global
-// ticket counter (zeroed on the launch stream). SQP iteration counts are heavy-tailed (a few % of the IK problems run
-// to max_iterations), so a static stride leaves most warps idle while the unlucky ones finish.
-__device__ __forceinline__ long long next_ticket(unsigned long long* __restrict__ ctr) {
-  unsigned long long t = 0;
-  if ((threadIdx.x & 31) == 0) t = atomicAdd(ctr, 1ULL);
-  t = __shfl_sync(0xffffffffu, t, 0);
-  return (long long)gridDim.x + (long long)t;
-}
-
-__global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out,
-                                                                      unsigned long long* __restrict__ ticket) {
+// LOCK-STEP schedule: W warps per CTA, each warp owns one problem at a time (ticket queue), and the warps of a CTA walk the
+// phases of an SQP iteration TOGETHER: [fetch] | linearize (FK + Jacobians + J'J) | inner QP | derivatives + line search +
+// lambda update, one CTA barrier after each. Why: the one-warp-per-CTA kernel walks ~5K instructions = 80 KB of text per SQP
+// iteration against a 32 KB L1.5 instruction cache with its 16 resident warps each somewhere else in that text -- measured
+// ~28 cycles per issued warp instruction, an L2 round trip per fetched line (profiles/r01_ik6_ncu_full_summary.txt:
+// stall_no_instruction 9.8 per issue). In lock-step a fetched line serves W warps, and the loops inside a phase (Newton steps of
+// the QP, line search evaluations) have bodies that fit the cache once nobody else is evicting them. The arithmetic of a
+// problem is untouched: results are bit-identical to the W = 1 schedule. Cost: warps idle at the barriers while the slowest
+// QP / line search of the CTA finishes.
+template <int W, int MINB>
+__global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out,
+                                                                    unsigned long long* __restrict__ ticket,
+                                                                    const long long per_warp_doubles) {
   extern __shared__ double smem[];
-  const int lane = threadIdx.x, n = a.n, k = a.n_eq, m = a.m;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n = a.n, k = a.n_eq, m = a.m;
   ChainWork C;
-  double* q = chain_carve(C, smem, a.links, n);
-  GenWork W;
-  gen_carve(W, q, n, k, m, 32);
+  double* q = chain_carve(C, smem + (long long)warp * per_warp_doubles, a.links, n);
+  GenWork W_;
+  gen_carve(W_, q, n, k, m, 32);
   const bool null_space = m == 0 && k > 0;  // solver choice of the reference, nonlinear.cc:83-89
   double* nswork = q;                       // QPNullSpaceSolver workspace aliases the interior point workspace
   q += (null_space && ns_smem_doubles(n, k) > gen_smem_doubles(n, k, m, 32)) ? ns_smem_doubles(n, k) : gen_smem_doubles(n, k, m, 32);
@@ -464,44 +463,87 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
   double* re = q; q += kMaxChainRows;
   double* err = q; q += 8;
   chain_setup(C, a);
-  for (int i = lane; i < m; i += 32) { W.cv[i] = a.ineq_var[i]; W.ca[i] = a.ineq_a[i]; }
+  for (int i = lane; i < m; i += 32) { W_.cv[i] = a.ineq_var[i]; W_.ca[i] = a.ineq_a[i]; }
   __syncwarp();
   GenProb Q{G, cvec, k ? A : nullptr, k ? bvec : nullptr};
   const GenSolveParams sp{1.0, 0.1, prm.kkt_tol, 1.0e-6, prm.max_qp_iterations, MO_BARRIER_COMPLEMENTARITY, 0,
                           k ? MO_GUESS_SOLVE_EQUALITY_CONSTRAINED : MO_GUESS_NAIVE, 0};  // nonlinear.cc:226-239
   constexpr int kMaxSteps = 40;
-  for (long long p = blockIdx.x; p < a.batch; p = next_ticket(ticket)) {
-    if (lane == 0) *C.have_cache = 0;
-    for (int i = lane; i < n; i += 32) x[i] = a.x0[p * n + i];
+  // state of this warp's problem (uniform over the lanes)
+  long long p = -1;
+  bool busy = false, drained = false;
+  int state = 0, term = MO_NLS_MAX_ITERATIONS, iters = 0, qp_total = 0, ls_total = 0, iter = 0;
+  double lambda = 0.0, penalty = 0.0;
+  // results of problem p: x, the errors at x, the counters
+  auto finish = [&]() {
     __syncwarp();
-    int state = 0, term = MO_NLS_MAX_ITERATIONS, iters = 0, qp_total = 0, ls_total = 0;
-    double lambda = prm.lambda_initial, penalty = prm.equality_penalty_initial;
-    for (int iter = 0; iter < prm.max_iterations; ++iter) {
-      // ---- LinearizeAndFillQP ----
+    for (int i = lane; i < n; i += 32) out.x[p * n + i] = x[i];
+    double ff = 0.0, fe = 0.0;
+    if (out.errors) chain_errors(C, a, p, x, rc, ff, fe);
+    if (lane == 0) {
+      out.termination[p] = term;
+      out.iterations[p] = iters;
+      if (out.qp_iterations) out.qp_iterations[p] = qp_total;
+      if (out.ls_steps) out.ls_steps[p] = ls_total;
+      if (out.errors) { out.errors[2 * p] = ff; out.errors[2 * p + 1] = fe; }
+    }
+    __syncwarp();
+    busy = false;
+  };
+  for (;;) {
+    // ---- fetch: an idle warp takes the next problem of the batch ----
+    while (!busy && !drained) {
+      unsigned long long t = 0;
+      if (lane == 0) t = atomicAdd(ticket, 1ULL);
+      p = (long long)__shfl_sync(0xffffffffu, t, 0);
+      if (p >= a.batch) { drained = true; break; }
+      if (lane == 0) *C.have_cache = 0;
+      for (int i = lane; i < n; i += 32) x[i] = a.x0[p * n + i];
+      __syncwarp();
+      state = 0; term = MO_NLS_MAX_ITERATIONS; iters = 0; qp_total = 0; ls_total = 0; iter = 0;
+      lambda = prm.lambda_initial; penalty = prm.equality_penalty_initial;
+      busy = true;
+      if (prm.max_iterations <= 0) finish();  // the Solve loop never runs: MAX_ITERATIONS at x0
+    }
+    if (W > 1) { if (!__syncthreads_or(busy ? 1 : 0)) break; }
+    else if (!busy) break;
+    bool ended = false;  // this problem terminates in this pass
+    double pre_f = 0.0, pre_eq = 0.0;
+    // ---- phase A: LinearizeAndFillQP (nonlinear.cc:170-214) ----
+    if (busy) {
       chain_rows(C, x, a.n_cost, a.cost_w, a.cost_target + p * a.n_cost, rc, Jc);
       if (k) chain_rows(C, x, k, a.eq_w, a.eq_target + p * k, re, Je);
       linearize_warp(n, a.n_cost, a.cost_block, k, m, x, Jc, rc, Je, re, lambda, a.ineq_var, a.ineq_a, a.ineq_b, G, cvec,
-                     A, bvec, W.cb, err);
-      const double pre_f = err[0], pre_eq = err[1];
-      // ---- ComputeStepDirection (nonlinear.cc:216-259): Setup + Solve on the QP in shared memory ----
-      for (int i = lane; i < W.T; i += 32) W.vars[i] = 0.0;
+                     A, bvec, W_.cb, err);
+      pre_f = err[0]; pre_eq = err[1];
+    }
+    if (W > 1) __syncthreads();
+    // ---- phase B: ComputeStepDirection (nonlinear.cc:216-259): Setup + Solve on the QP in shared memory ----
+    if (busy) {
+      for (int i = lane; i < W_.T; i += 32) W_.vars[i] = 0.0;
       __syncwarp();
       int qiters = 0;
       double kkt_after[4];
       if (null_space) {  // QPNullSpaceSolver (qp.cc:679-729); dx = 0 unless SUCCESS (nonlinear.cc:248-258)
         const int ns = ns_solve_warp(n, k, G, cvec, A, bvec, dx, nswork);
-        if (ns == 1) { term = MO_NLS_QP_INDEFINITE; break; }  // QPWasIndefinite, nonlinear.cc:103-105
-        if (ns != 0) { term = MO_NLS_QP_FAILED; break; }
-        qp_total += 1;  // NumQPIterations counts one per null-space solve (structs.cc:208-219)
+        if (ns == 1) { term = MO_NLS_QP_INDEFINITE; ended = true; }  // QPWasIndefinite, nonlinear.cc:103-105
+        else if (ns != 0) { term = MO_NLS_QP_FAILED; ended = true; }
+        else qp_total += 1;  // NumQPIterations counts one per null-space solve (structs.cc:208-219)
       } else {
-        int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve_any(W, Q, sp, qiters, kkt_after);
-        if (qstatus < 0) qstatus = gen_solve<32>(W, Q, sp, nullptr, qiters, kkt_after);
-        if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; break; }  // the reference throws here
-        qp_total += qiters;
-        for (int i = lane; i < n; i += 32) dx[i] = W.vars[i];
+        int qstatus = prm.inner_qp_solver == MO_NLS_QP_GENERIC ? -1 : wip_solve_any(W_, Q, sp, qiters, kkt_after);
+        if (qstatus < 0) qstatus = gen_solve<32>(W_, Q, sp, nullptr, qiters, kkt_after);
+        if (qstatus >= MO_QP_FAILED_FACTORIZATION) { term = MO_NLS_QP_FAILED; ended = true; }  // the reference throws here
+        else {
+          qp_total += qiters;
+          for (int i = lane; i < n; i += 32) dx[i] = W_.vars[i];
+        }
       }
       __syncwarp();
-      // ---- ComputeQPCostDerivative (:457-482), SelectPenalty (:484-502) ----
+    }
+    if (W > 1) __syncthreads();
+    // ---- phase C: derivatives, penalty, line search, lambda update ----
+    if (busy && !ended) {
+      // ComputeQPCostDerivative (:457-482), SelectPenalty (:484-502)
       double d_f = 0.0, d_eq = 0.0;
       for (int i = 0; i < n; ++i) d_f += cvec[i] * dx[i];
       for (int r = 0; r < k; ++r) {
@@ -522,18 +564,17 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
         const double np = (d_f + 0.5 * fmax(0.0, quad)) / ((1 - prm.equality_penalty_rho) * l1);
         if (np > penalty) penalty = np * prm.equality_penalty_scale_factor;
       } else if (k) {
-        const double* y = W.vars + n + m;
+        const double* y = W_.vars + n + m;
         double linf = fabs(y[0]);
         for (int r = 1; r < k; ++r) linf = fmax(linf, fabs(y[r]));
         if (linf > penalty) penalty = linf * prm.equality_penalty_scale_factor;
       }
-      // ---- SelectStepSize (:351-416) ----
+      // SelectStepSize (:351-416)
       const double dd_total = d_f + penalty * d_eq, dd_linf = fmax(fabs(d_f), fabs(d_eq));
       const double phi0 = pre_f + penalty * pre_eq;
       int step_result = 1;  // 0 SUCCESS 1 MAX_ITERATIONS 2 FIRST_ORDER_SATISFIED 3 POSITIVE_DERIVATIVE 4 NON_FINITE 5 INVALID_ALPHA
       double alpha = 1.0, last_f = 0.0, last_eq = 0.0;
       double a_prev = 0.0, phi_prev = 0.0, a_prev2 = 0.0, phi_prev2 = 0.0;  // last two logged steps
-      int nsteps = 0;
       for (int it = 0; it <= prm.max_line_search_iterations && it < kMaxSteps; ++it) {
         if (prm.line_search_strategy == MO_LS_POLYNOMIAL_APPROXIMATION) {
           if (it > 0) {
@@ -568,14 +609,13 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
         chain_errors(C, a, p, cand, rc, last_f, last_eq);
         a_prev2 = a_prev; phi_prev2 = phi_prev;
         a_prev = alpha; phi_prev = last_f + penalty * last_eq;
-        ++nsteps;
         ++ls_total;
         if (!isfinite(last_f) || !isfinite(last_eq)) { step_result = 4; break; }
         if (dd_linf < prm.absolute_first_derivative_tol) { step_result = 2; break; }
         else if (dd_total > 0) { step_result = 3; break; }
         if (phi_prev <= phi0 + dd_total * alpha * 1.0e-4) { step_result = 0; break; }
       }
-      // ---- UpdateLambdaAndCheckExitConditions (:296-343) ----
+      // UpdateLambdaAndCheckExitConditions (:296-343)
       int exit_state = -1;
       if (step_result == 0) {
         __syncwarp();
@@ -593,20 +633,11 @@ __global__ void __launch_bounds__(32, MO_IK_MINB) nls_chain_ik_kernel(const Chai
         if (lambda > prm.max_lambda) exit_state = MO_NLS_MAX_LAMBDA;
       }
       ++iters;
-      if (exit_state >= 0) { term = exit_state; break; }
+      ++iter;
+      if (exit_state >= 0) { term = exit_state; ended = true; }
+      else if (iter >= prm.max_iterations) ended = true;  // term stays MAX_ITERATIONS
     }
-    __syncwarp();
-    for (int i = lane; i < n; i += 32) out.x[p * n + i] = x[i];
-    double ff = 0.0, fe = 0.0;
-    if (out.errors) chain_errors(C, a, p, x, rc, ff, fe);
-    if (lane == 0) {
-      out.termination[p] = term;
-      out.iterations[p] = iters;
-      if (out.qp_iterations) out.qp_iterations[p] = qp_total;
-      if (out.ls_steps) out.ls_steps[p] = ls_total;
-      if (out.errors) { out.errors[2 * p] = ff; out.errors[2 * p + 1] = fe; }
-    }
-    __syncwarp();
+    if (busy && ended) finish();
   }
 }
 

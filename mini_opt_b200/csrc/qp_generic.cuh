@@ -16,6 +16,11 @@
 
 namespace mo {
 
+// Index of this thread inside its problem's team: the lane for THREADS == 32 (several one-warp teams may share a CTA,
+// e.g. the lock-step IK kernel), threadIdx.x for the one-CTA-per-problem instantiations.
+template <int THREADS>
+__device__ __forceinline__ int team_tid() { return THREADS == 32 ? (int)(threadIdx.x & 31) : (int)threadIdx.x; }
+
 template <int THREADS>
 __device__ __forceinline__ void block_sync() {
   if (THREADS == 32) __syncwarp(); else __syncthreads();
@@ -103,7 +108,7 @@ struct GenWork {
 // as Eigen's ldlt_inplace<Lower>::unblocked). Returns true on success (Eigen's `ret`), uniformly.
 template <int THREADS>
 __device__ bool gen_ldlt_factor(const GenWork& W) {
-  const int tid = threadIdx.x, size = W.p;
+  const int tid = team_tid<THREADS>(), size = W.p;
   bool found_zero_pivot = false, ret = true;
   if (size <= 1) {
     if (size == 1 && tid == 0) W.transp[0] = 0;
@@ -170,7 +175,7 @@ __device__ bool gen_ldlt_factor(const GenWork& W) {
 // Solve Kmat * x = rhs in place with the factors above (Eigen LDLT::_solve_impl_transposed, LDLT.h:574-611).
 template <int THREADS>
 __device__ void gen_ldlt_solve(const GenWork& W, double* x) {
-  const int tid = threadIdx.x, size = W.p;
+  const int tid = team_tid<THREADS>(), size = W.p;
   if (tid == 0) {
     for (int i = 0; i < size; ++i) { const int t = W.transp[i]; if (t != i) { const double v = x[i]; x[i] = x[t]; x[t] = v; } }
   }
@@ -236,7 +241,7 @@ struct GenProb {
 // EvaluateKKTConditions, qp.cc:391-420. The symmetric product reads only the lower triangle of G.
 template <int THREADS>
 __device__ void gen_eval_kkt(const GenWork& W, const GenProb& Q, bool with_ineq) {
-  const int tid = threadIdx.x, n = W.n, k = W.k, m = W.m;
+  const int tid = team_tid<THREADS>(), n = W.n, k = W.k, m = W.m;
   const double *x = GX(W), *s = GS(W), *y = GY(W), *z = GZ(W);
   double *r_d = W.r, *r_comp = W.r + n, *r_pe = W.r + n + m, *r_pi = W.r + n + m + k;
   for (int i = tid; i < n; i += THREADS) {
@@ -276,7 +281,7 @@ __device__ void gen_eval_kkt(const GenWork& W, const GenProb& Q, bool with_ineq)
 // Returns 0, MO_QP_NONPOSITIVE_SLACK or MO_QP_FAILED_FACTORIZATION (uniform).
 template <int THREADS>
 __device__ int gen_compute_ldlt(const GenWork& W, const GenProb& Q, bool with_ineq) {
-  const int tid = threadIdx.x, n = W.n, k = W.k, m = W.m, p = W.p;
+  const int tid = team_tid<THREADS>(), n = W.n, k = W.k, m = W.m, p = W.p;
   const double *s = GS(W), *z = GZ(W);
   if (with_ineq) {
     double bad = 0.0;
@@ -314,7 +319,7 @@ __device__ int gen_compute_ldlt(const GenWork& W, const GenProb& Q, bool with_in
 // SolveForUpdate (qp.cc:318-364) / SolveForUpdateNoInequalities (:366-386): delta <- Newton direction.
 template <int THREADS>
 __device__ void gen_solve_for_update(const GenWork& W, double mu, bool with_ineq) {
-  const int tid = threadIdx.x, n = W.n, k = W.k, m = W.m;
+  const int tid = team_tid<THREADS>(), n = W.n, k = W.k, m = W.m;
   const double *s = GS(W);
   const double *r_d = W.r, *r_comp = W.r + n, *r_pe = W.r + n + m, *r_pi = W.r + n + m + k;
   const double *ds_aff = W.daff + n, *dz_aff = W.daff + n + m + k;
@@ -350,7 +355,7 @@ __device__ void gen_solve_for_update(const GenWork& W, double mu, bool with_ineq
 template <int THREADS>
 __device__ double gen_compute_alpha(const GenWork& W, const double* val, const double* dval, double tau) {
   double alpha = 1.0;
-  for (int i = threadIdx.x; i < W.m; i += THREADS) {
+  for (int i = team_tid<THREADS>(); i < W.m; i += THREADS) {
     const double updated = val[i] + dval[i];
     if (updated <= 0.0 && fabs(dval[i]) > 0) alpha = fmin(alpha, -tau * val[i] / dval[i]);
   }
@@ -363,14 +368,14 @@ __device__ double gen_compute_mu(const GenWork& W) {
   if (W.m == 0) return 0.0;
   const double *s = GS(W), *z = GZ(W);
   double acc = 0.0;
-  for (int i = threadIdx.x; i < W.m; i += THREADS) acc += s[i] * z[i];
+  for (int i = team_tid<THREADS>(); i < W.m; i += THREADS) acc += s[i] * z[i];
   return block_sum<THREADS>(acc, W.scratch) / (double)W.m;
 }
 
 // ComputeErrors, qp.cc:423-437 -> {r_dual, r_comp, r_primal_eq, r_primal_ineq}
 template <int THREADS>
 __device__ void gen_compute_errors(const GenWork& W, double mu, double (&out)[4]) {
-  const int tid = threadIdx.x, n = W.n, k = W.k, m = W.m;
+  const int tid = team_tid<THREADS>(), n = W.n, k = W.k, m = W.m;
   const double *r_d = W.r, *r_comp = W.r + n, *r_pe = W.r + n + m, *r_pi = W.r + n + m + k;
   double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
   for (int i = tid; i < n; i += THREADS) a0 += r_d[i] * r_d[i];
@@ -395,7 +400,7 @@ __device__ __forceinline__ double max4(const double (&e)[4]) { return fmax(fmax(
 // Returns 0 or a failure status (state untouched on failure).
 template <int THREADS>
 __device__ int gen_iterate(const GenWork& W, const GenProb& Q, double mu_input, int strategy, double (&ip)[6]) {
-  const int tid = threadIdx.x, n = W.n, k = W.k, m = W.m;
+  const int tid = team_tid<THREADS>(), n = W.n, k = W.k, m = W.m;
   gen_eval_kkt<THREADS>(W, Q, true);
   ip[0] = mu_input; ip[1] = 1.0; ip[2] = 1.0; ip[3] = qnan(); ip[4] = qnan(); ip[5] = qnan();
   const int st = gen_compute_ldlt<THREADS>(W, Q, true);
@@ -452,7 +457,7 @@ __device__ void gen_bind(const QPArgs& a, long long prob, double* smem, GenWork&
   Q.A = k ? a.A + prob * (long long)k * n : nullptr;
   Q.b = k ? a.b + prob * (long long)k : nullptr;
   const bool box = (a.flags & MO_QP_FLAG_BOX_PAIRS) != 0;
-  for (int i = threadIdx.x; i < m; i += THREADS) {
+  for (int i = team_tid<THREADS>(); i < m; i += THREADS) {
     W.cv[i] = box ? i / 2 : a.ivar[prob * mmax + i];
     W.ca[i] = box ? ((i & 1) ? -1.0 : 1.0) : a.ia[prob * mmax + i];
     W.cb[i] = a.ib[prob * mmax + i];
@@ -464,27 +469,27 @@ __device__ void gen_bind(const QPArgs& a, long long prob, double* smem, GenWork&
 template <int THREADS>
 __device__ void gen_store_vars(const GenWork& W, int mmax, const double* v, double* dst) {
   const int n = W.n, k = W.k, m = W.m;
-  for (int i = threadIdx.x; i < n; i += THREADS) dst[i] = v[i];
-  for (int i = threadIdx.x; i < mmax; i += THREADS) {
+  for (int i = team_tid<THREADS>(); i < n; i += THREADS) dst[i] = v[i];
+  for (int i = team_tid<THREADS>(); i < mmax; i += THREADS) {
     dst[n + i] = i < m ? v[n + i] : qnan();
     dst[n + mmax + k + i] = i < m ? v[n + m + k + i] : qnan();
   }
-  for (int i = threadIdx.x; i < k; i += THREADS) dst[n + mmax + i] = v[n + m + i];
+  for (int i = team_tid<THREADS>(); i < k; i += THREADS) dst[n + mmax + i] = v[n + m + i];
 }
 
 template <int THREADS>
 __device__ void gen_load_vars(const GenWork& W, int mmax, const double* src, double* v) {
   const int n = W.n, k = W.k, m = W.m;
-  for (int i = threadIdx.x; i < n; i += THREADS) v[i] = src[i];
-  for (int i = threadIdx.x; i < m; i += THREADS) { v[n + i] = src[n + i]; v[n + m + k + i] = src[n + mmax + k + i]; }
-  for (int i = threadIdx.x; i < k; i += THREADS) v[n + m + i] = src[n + mmax + i];
+  for (int i = team_tid<THREADS>(); i < n; i += THREADS) v[i] = src[i];
+  for (int i = team_tid<THREADS>(); i < m; i += THREADS) { v[n + i] = src[n + i]; v[n + m + k + i] = src[n + mmax + k + i]; }
+  for (int i = team_tid<THREADS>(); i < k; i += THREADS) v[n + m + i] = src[n + mmax + i];
   block_sync<THREADS>();
 }
 
 // ComputeInitialGuess, qp.cc:439-482. Returns 0 or a failure status.
 template <int THREADS>
 __device__ int gen_initial_guess(const GenWork& W, const GenProb& Q, int method) {
-  const int tid = threadIdx.x, n = W.n, k = W.k, m = W.m;
+  const int tid = team_tid<THREADS>(), n = W.n, k = W.k, m = W.m;
   if (method == MO_GUESS_USER_PROVIDED) return 0;
   double *x = GX(W), *s = GS(W), *y = GY(W), *z = GZ(W);
   for (int i = tid; i < n; i += THREADS) x[i] = 0.0;
@@ -529,7 +534,7 @@ struct GenSolveParams {
 template <int THREADS>
 __device__ int gen_solve(const GenWork& W, const GenProb& Q, const GenSolveParams& a, double* log, int& iters,
                          double (&kkt_after)[4]) {
-  const int tid = threadIdx.x;
+  const int tid = team_tid<THREADS>();
   int status = gen_initial_guess<THREADS>(W, Q, a.guess);
   iters = 0;
   double kkt_prev[4] = {0, 0, 0, 0}, ip[6];
@@ -564,7 +569,7 @@ __device__ int gen_solve(const GenWork& W, const GenProb& Q, const GenSolveParam
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) qp_ip_generic_kernel(const QPArgs a) {
   extern __shared__ double smem[];
-  const int tid = threadIdx.x;
+  const int tid = team_tid<THREADS>();
   const long long vstride = a.n + 2LL * a.m + a.k;
   const GenSolveParams sp{a.initial_mu, a.sigma, a.kkt_tol, a.comp_tol, a.max_iterations, a.strategy,
                           a.decrease_mu_only_on_small_error, a.guess, a.init_mu_with_comp};
@@ -603,7 +608,7 @@ __global__ void __launch_bounds__(THREADS) qp_ip_generic_kernel(const QPArgs a) 
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) qp_ip_generic_step_kernel(const QPArgs a, const StepArgs sa) {
   extern __shared__ double smem[];
-  const int tid = threadIdx.x;
+  const int tid = team_tid<THREADS>();
   const long long vstride = a.n + 2LL * a.m + a.k;
   for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
     GenWork W;

@@ -241,7 +241,7 @@ __device__ inline int ns_solve_warp(int n, int k, const double* __restrict__ G, 
   return 0;
 }
 
-__global__ void __launch_bounds__(32) qp_nullspace_kernel(const NullSpaceArgs a) {
+static __global__ void __launch_bounds__(32) qp_nullspace_kernel(const NullSpaceArgs a) {
   extern __shared__ double ns_smem[];
   const int n = a.n, k = a.k;
   for (long long p = blockIdx.x; p < a.batch; p += gridDim.x) {
