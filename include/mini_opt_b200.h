@@ -375,9 +375,11 @@ int mo_debug_set_tma(int enabled);
 /* Measurement / cross-check hook: 0 = default kernel for the DMMA shapes (warp per problem, "dmma_warp"), 1 = the
  * CTA-per-problem kernel ("dmma_cta"). Returns the previous value. Process-wide; the library reads no environment. */
 int mo_debug_set_dm_kernel(int which);
-/* Measurement hook: warps per CTA of the lock-step chain-IK kernel (1, 2, 4, 8, 16; -1 on anything else). Results are
- * bit-identical for every value. Returns the previous value. */
+/* Measurement hooks of the lock-step chain-IK kernel: warps per CTA (1, 4, 8, 16; -1 on anything else) and which of the
+ * two optional CTA barriers of a pass are taken (bit 0: after the linearization, bit 1: after the inner QP). Results are
+ * bit-identical for every value. Each returns the previous value. */
 int mo_debug_set_ik_warps(int warps);
+int mo_debug_set_ik_sync(int mask);
 
 #ifdef __cplusplus
 } /* extern "C" */

@@ -440,7 +440,7 @@ __device__ unsigned long long g_ik_tickets[kIkTicketSlots];
 template <int W, int MINB>
 __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out,
                                                                     unsigned long long* __restrict__ ticket,
-                                                                    const long long per_warp_doubles) {
+                                                                    const long long per_warp_doubles, const int sync_mask) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n = a.n, k = a.n_eq, m = a.m;
   ChainWork C;
@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
                      A, bvec, W_.cb, err);
       pre_f = err[0]; pre_eq = err[1];
     }
-    if (W > 1) __syncthreads();
+    if (W > 1 && (sync_mask & 1)) __syncthreads();  // uniform over the CTA: a kernel argument
     // ---- phase B: ComputeStepDirection (nonlinear.cc:216-259): Setup + Solve on the QP in shared memory ----
     if (busy) {
       for (int i = lane; i < W_.T; i += 32) W_.vars[i] = 0.0;
@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
       }
       __syncwarp();
     }
-    if (W > 1) __syncthreads();
+    if (W > 1 && (sync_mask & 2)) __syncthreads();
     // ---- phase C: derivatives, penalty, line search, lambda update ----
     if (busy && !ended) {
       // ComputeQPCostDerivative (:457-482), SelectPenalty (:484-502)

@@ -12,6 +12,10 @@ namespace {
 #define MO_IK_WARPS 16
 #endif
 std::atomic<int> g_ik_warps{MO_IK_WARPS};  // mo_debug_set_ik_warps
+#ifndef MO_IK_SYNC
+#define MO_IK_SYNC 3
+#endif
+std::atomic<int> g_ik_sync{MO_IK_SYNC};    // mo_debug_set_ik_sync: CTA barriers after phase A (1) and phase B (2)
 
 int cuda_err(cudaError_t e, const char* what, std::string* err) {
   *err = std::string(what) + ": " + cudaGetErrorString(e);
@@ -113,7 +117,7 @@ int nls_launch_chain_ik(const mo_chain_ik_batch* problems, const mo_nls_params* 
     int grid = 0;
     const int rc = block_grid(kernel, 32 * warps, smem, (problems->batch + warps - 1) / warps, dev, &grid, err);
     if (rc) return rc;
-    kernel<<<grid, 32 * warps, smem, stream>>>(ca, p, o, tickets, per_warp);
+    kernel<<<grid, 32 * warps, smem, stream>>>(ca, p, o, tickets, per_warp, g_ik_sync.load());
     NLS_CUDA(cudaGetLastError());
     return MO_OK;
   };
@@ -124,7 +128,6 @@ int nls_launch_chain_ik(const mo_chain_ik_batch* problems, const mo_nls_params* 
     case 16: return launch(nls_chain_ik_kernel<16, 1>, 16);
     case 8: return launch(nls_chain_ik_kernel<8, 2>, 8);
     case 4: return launch(nls_chain_ik_kernel<4, 4>, 4);
-    case 2: return launch(nls_chain_ik_kernel<2, 8>, 2);
     default: return launch(nls_chain_ik_kernel<1, 16>, 1);
   }
 }
@@ -134,6 +137,10 @@ int nls_launch_chain_ik(const mo_chain_ik_batch* problems, const mo_nls_params* 
 // Measurement hook: warps per CTA of the lock-step chain-IK kernel (1, 2, 4, 8 or 16; 1 = every warp on its own, the
 // round-1 schedule). Returns the previous value. Results do not depend on it (bit-identical), only the time does.
 extern "C" int mo_debug_set_ik_warps(int warps) {
-  if (warps != 1 && warps != 2 && warps != 4 && warps != 8 && warps != 16) return -1;
+  if (warps != 1 && warps != 4 && warps != 8 && warps != 16) return -1;
   return mo::g_ik_warps.exchange(warps);
 }
+
+// Measurement hook: which of the two optional CTA barriers of a lock-step pass are taken (bit 0: after the linearization,
+// bit 1: after the inner QP); the barrier at the top of a pass always is. Results do not depend on it.
+extern "C" int mo_debug_set_ik_sync(int mask) { return mo::g_ik_sync.exchange(mask & 3); }

@@ -19,8 +19,9 @@ ch = nls.chain_to_device(synth.chain_ik_batch_numpy(a.links, a.batch, seed=4321,
 prm = synth.chain_ik_params()
 res = {"links": a.links, "batch": a.batch, "n_eq": a.n_eq, "runs": []}
 ref = None
-for w in (1, 2, 4, 8, 16, 1, 8):
+for w, mask in ((1, 3), (8, 3), (16, 3), (16, 2), (16, 1), (16, 0), (8, 0), (8, 2)):
     assert L.mo_debug_set_ik_warps(w) >= 1
+    L.mo_debug_set_ik_sync(mask)
     out = nls.alloc_nls_out_torch(a.batch, ch.n, dev)
     nls.solve_chain_ik_device(ch, prm, out, dev)
     torch.cuda.synchronize()
@@ -35,7 +36,8 @@ for w in (1, 2, 4, 8, 16, 1, 8):
     if ref is None:
         ref = cur
     same = all((getattr(cur, f) == getattr(ref, f)).all() for f in ("x", "termination", "iterations", "qp_iterations", "ls_steps"))
-    res["runs"].append({"warps_per_cta": w, "ms": ms, "problems_per_s": a.batch / (ms * 1e-3),
+    res["runs"].append({"warps_per_cta": w, "sync_mask": mask, "ms": ms, "problems_per_s": a.batch / (ms * 1e-3),
                         "qp_steps_per_s": float(cur.qp_iterations.sum()) / (ms * 1e-3), "bit_identical_to_first": bool(same)})
 L.mo_debug_set_ik_warps(16)
+L.mo_debug_set_ik_sync(3)
 print(json.dumps(res))
