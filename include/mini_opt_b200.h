@@ -372,6 +372,9 @@ int mo_abi_version(void);
 /* Measurement hook (profiles/, tests): staging mode of the kernels that load per-problem arrays with TMA bulk copies
  * (cp.async.bulk + mbarrier). 1 = TMA (default), 0 = plain per-lane loads. Returns the previous value. Process-wide. */
 int mo_debug_set_tma(int enabled);
+/* Measurement hook: refill of the thread-per-problem kernel through cp.async one round ahead (1, default) or through
+ * registers (0, the round-1 schedule). Results are bit-identical. Returns the previous value. */
+int mo_debug_set_tpp_async(int enabled);
 /* Measurement / cross-check hook: 0 = default kernel for the DMMA shapes (warp per problem, "dmma_warp"), 1 = the
  * CTA-per-problem kernel ("dmma_cta"). Returns the previous value. Process-wide; the library reads no environment. */
 int mo_debug_set_dm_kernel(int which);

@@ -21,6 +21,11 @@ namespace {
 
 thread_local std::string g_last_error;
 std::atomic<long long> g_launches{0};
+#ifndef MO_TPP_ASYNC
+#define MO_TPP_ASYNC 1
+#endif
+// refill of the tpp kernel: 1 = cp.async into the idle lane's column one round ahead (default), 0 = LDG/STS (A/B, mo_debug_set_tpp_async)
+static std::atomic<int> g_tpp_async{MO_TPP_ASYNC};
 // staging mode of the warp16 kernel: 1 = TMA bulk copies (default), 0 = lane loads (A/B measurements, mo_debug_set_tma)
 std::atomic<int> g_w16_tma{1};
 
@@ -146,14 +151,13 @@ constexpr int kTppMinBlocks = 2;
 // (N, K) shapes with a thread-per-problem instantiation (box pairs, m == 2n, uniform count).
 #define MO_TPP_SHAPES(X) X(8, 2) X(8, 0) X(4, 1)
 
-template <int N, int K>
-int launch_tpp(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
-  using L = mo::TppLayout<N, K>;
+template <int N, int K, bool ASYNC>
+int launch_tpp_impl(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
   constexpr int threads = 32 * kTppWarpsPerBlock;
   auto guess = mo::qp_tpp_guess_kernel<N, K>;
-  auto iterate = mo::qp_tpp_iterate_kernel<N, K, kTppWarpsPerBlock, kTppMinBlocks>;
+  auto iterate = mo::qp_tpp_iterate_kernel<N, K, kTppWarpsPerBlock, kTppMinBlocks, ASYNC>;
   const size_t smem_guess = 0;
-  const size_t smem_iter = sizeof(double) * L::ETOT * (threads + 1);
+  const size_t smem_iter = mo::tpp_iterate_smem_bytes<N, K, kTppWarpsPerBlock>(ASYNC);
   static thread_local int configured_dev = -1;
   static thread_local int bps_guess = 0, bps_iter = 0;
   int cur = 0;
@@ -178,6 +182,11 @@ int launch_tpp(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) 
   g_launches.fetch_add(1);
   MO_CUDA(cudaGetLastError());
   return MO_OK;
+}
+
+template <int N, int K>
+int launch_tpp(const mo::QPArgs& a, const DeviceInfo& dev, cudaStream_t stream) {
+  return g_tpp_async.load() ? launch_tpp_impl<N, K, true>(a, dev, stream) : launch_tpp_impl<N, K, false>(a, dev, stream);
 }
 
 bool tpp_eligible(int n, int k, int m, int flags, bool ragged, int strategy) {
@@ -358,6 +367,7 @@ int64_t mo_qp_vars_stride(int32_t n, int32_t k, int32_t m) { return (int64_t)n +
 int mo_abi_version(void) { return MO_ABI_VERSION; }
 
 int mo_debug_set_tma(int enabled) { return g_w16_tma.exchange(enabled ? 1 : 0); }
+int mo_debug_set_tpp_async(int enabled) { return g_tpp_async.exchange(enabled ? 1 : 0); }
 
 int mo_debug_set_dm_kernel(int which) { return g_dm_kernel.exchange(which == 1 ? 1 : 0); }
 

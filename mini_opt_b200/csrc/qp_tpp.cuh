@@ -295,7 +295,31 @@ __global__ void __launch_bounds__(128) qp_tpp_guess_kernel(const QPArgs a) {
 // ---------------------------------------------------------------------------------------------
 // Kernel 2: the Newton loop (qp.cc:110-149) from the start state in `vars`.
 // ---------------------------------------------------------------------------------------------
-template <int N, int K, int WPB, int MINB>
+// ASYNC = true: the refill never waits for global memory. The inputs and the start state of a new problem are copied
+// with 8-byte cp.async requests (LDGSTS) straight into the idle lane's shared-memory column -- x, y into one of
+// XY_SLOTS staging rows of the warp -- while the other lanes compute; the lane joins the NEXT round (one idle round
+// per problem, ~9 % of the lane rounds at 11 Newton steps per QP) after a cp.async.wait_group that has long been
+// satisfied. ASYNC = false is the round-1 refill (LDG into registers, then STS: a global round trip in nearly every
+// round, 37 % of the samples of profiles/r02_tpp_n8_ncu_full_summary.txt), kept for the A/B (mo_debug_set_tpp_async).
+constexpr int kTppXYSlots = 6;  // new problems per warp per round; what the 2 x 114 KB CTAs leave free on an SM
+
+__device__ __forceinline__ void tpp_cp8(double* smem_dst, const double* gsrc) {
+  const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+// predicated form on a 32-bit shared address: no branch around the copy
+__device__ __forceinline__ void tpp_cp8_if(bool pred, unsigned sdst, const double* gsrc) {
+  asm volatile("{ .reg .pred p; setp.ne.b32 p, %2, 0; @p cp.async.ca.shared.global [%0], [%1], 8; }" ::"r"(sdst), "l"(gsrc),
+               "r"((int)pred) : "memory");
+}
+
+template <int N, int K, int WPB>
+constexpr size_t tpp_iterate_smem_bytes(bool async) {
+  return sizeof(double) * (TppLayout<N, K>::ETOT * (32 * WPB + 1) + (async ? WPB * kTppXYSlots * (N + K) : 0));
+}
+
+template <int N, int K, int WPB, int MINB, bool ASYNC>
 __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QPArgs a, const int skip_failed) {
   using L = TppLayout<N, K>;
   constexpr int P = L::P, M = L::M, LD = 32 * WPB + 1, STRIDE = L::STRIDE;
@@ -322,12 +346,74 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
   long long prob = -1;
   int iters = 0;
   bool live = false, fin = false, first = false;
+  bool loading = false;  // ASYNC: copies of this lane's next problem are in flight
+  int st_in = -1, xy_slot = 0;
+  double* const xy_stage = smem + L::ETOT * LD + warp * (kTppXYSlots * (N + K));  // ASYNC only
+  // ASYNC: what this lane copies for EVERY new problem of its warp is fixed -- element u * 32 + lane of G, of the
+  // [A | c | b | bounds] run and of the start state -- so sources (array, per-problem stride, offset) and destinations
+  // (byte offset inside the column, or inside the x / y staging row: bit 31 set) are computed once.
+  constexpr int GLc = (N * N + 31) / 32, RESTc = N * K + N + K + M, RLc = (RESTc + 31) / 32, VLc = (STRIDE + 31) / 32;
+  int g_dst[GLc], v_dst[VLc], w_slot[VLc];
+  const double* r_src[RLc];
+  int r_stride[RLc];
+  const unsigned warp_s = static_cast<unsigned>(__cvta_generic_to_shared(smwarp));
+  const unsigned stage_s = static_cast<unsigned>(__cvta_generic_to_shared(xy_stage));
+  if constexpr (ASYNC) {
+#pragma unroll
+    for (int u = 0; u < GLc; ++u) {
+      const int e = u * 32 + lane, cc = e / N, rr = e - cc * N;  // column-major (rr, cc)
+      g_dst[u] = (e < N * N && rr >= cc) ? (L::OG + lidx(rr, cc)) * LD * 8 : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < RLc; ++u) {
+      const int e = u * 32 + lane;
+      r_src[u] = nullptr;
+      r_stride[u] = 0;
+      if (e < RESTc) {
+        if (K > 0 && e < N * K) { r_src[u] = a.A + e; r_stride[u] = N * K; }
+        else if (e < N * K + N) { r_src[u] = a.c + (e - N * K); r_stride[u] = N; }
+        else if (K > 0 && e < N * K + N + K) { r_src[u] = a.b + (e - N * K - N); r_stride[u] = K; }
+        else { r_src[u] = a.ib + (e - N * K - N - K); r_stride[u] = M; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VLc; ++u) {
+      const int e = u * 32 + lane;
+      int d = -1, w = -1;
+      if (e < N) { d = (int)(0x80000000u | (unsigned)(e * 8)); w = e; }
+      else if (e < N + M) { d = (L::OS + (e - N)) * LD * 8; w = L::OS + (e - N); }
+      else if (e < N + M + K) { d = (int)(0x80000000u | (unsigned)((N + e - N - M) * 8)); w = N + (e - N - M); }
+      else if (e < STRIDE) { d = (L::OZ + (e - N - M - K)) * LD * 8; w = L::OZ + (e - N - M - K); }
+      v_dst[u] = e < STRIDE ? d : 0;  // 0 is never a destination of the state (slot OG is G's)
+      w_slot[u] = e < STRIDE ? w * LD : -1;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < N; ++i) x[i] = 0.0;
 #pragma unroll
   for (int i = 0; i < KD; ++i) y[i] = 0.0;
 
   for (;;) {
+    if constexpr (ASYNC) {
+      // ======== (0) lanes whose copies were issued one round ago join ========
+      if (__any_sync(FULL, loading)) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        if (loading) {
+          const double* __restrict__ st = xy_stage + xy_slot * (N + K);
+#pragma unroll
+          for (int i = 0; i < N; ++i) x[i] = st[i];
+#pragma unroll
+          for (int r = 0; r < K; ++r) y[r] = st[N + r];
+          live = st_in != MO_QP_FAILED_FACTORIZATION;
+          first = true;
+          iters = 0;
+          alpha_p = 1.0; alpha_d = 1.0;
+          loading = false;
+        }
+        __syncwarp();  // the staging rows are free again
+      }
+    }
     // ======== (1) write out finished problems, refill idle lanes ========
     unsigned fmask = __ballot_sync(FULL, fin);
     while (fmask) {  // [x|s|y|z] of lane `src`: x, y parked in slots [0, N+K) of its column, s, z in place
@@ -336,18 +422,58 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
       const long long q = __shfl_sync(FULL, prob, src);
       double* __restrict__ vp = a.vars + q * STRIDE;
       const double* __restrict__ col = smwarp + src;
+      if constexpr (ASYNC) {
 #pragma unroll
-      for (int e0 = 0; e0 < STRIDE; e0 += 32) {
-        const int e = e0 + lane;
-        if (e < STRIDE) {
-          const int slot = e < N ? e : (e < N + M ? L::OS + (e - N) : (e < N + M + K ? N + (e - N - M) : L::OZ + (e - N - M - K)));
-          vp[e] = col[slot * LD];
+        for (int u = 0; u < VLc; ++u)
+          if (w_slot[u] >= 0) vp[u * 32 + lane] = col[w_slot[u]];
+      } else {
+#pragma unroll
+        for (int e0 = 0; e0 < STRIDE; e0 += 32) {
+          const int e = e0 + lane;
+          if (e < STRIDE) {
+            const int slot = e < N ? e : (e < N + M ? L::OS + (e - N) : (e < N + M + K ? N + (e - N - M) : L::OZ + (e - N - M - K)));
+            vp[e] = col[slot * LD];
+          }
         }
       }
     }
     fin = false;
     const unsigned idle = __ballot_sync(FULL, !live);
-    if (idle != 0u && next < wend) {
+    if (ASYNC && idle != 0u && next < wend) {
+      __syncwarp();  // the write-out above has read the columns that are about to be overwritten
+      const int rank = __popc(idle & ((1u << lane) - 1u));
+      const long long left = wend - next;
+      int cnt = __popc(idle);
+      cnt = cnt < kTppXYSlots ? cnt : kTppXYSlots;
+      cnt = (long long)cnt < left ? cnt : (int)left;
+      const bool take = !live && rank < cnt;
+      if (take) {
+        prob = next + rank;
+        xy_slot = rank;
+        st_in = skip_failed ? a.status[prob] : -1;
+      }
+      unsigned todo = __ballot_sync(FULL, take);
+      long long q = next;  // the taking lanes, in lane order, get consecutive problems and staging rows
+      next += cnt;
+      for (int sl = 0; todo; ++sl, ++q) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const unsigned col_s = warp_s + src * 8, row_s = stage_s + sl * ((N + K) * 8);
+        const double* __restrict__ Gp = a.G + q * (N * N) + lane;
+#pragma unroll
+        for (int u = 0; u < GLc; ++u) tpp_cp8_if(g_dst[u] >= 0, col_s + g_dst[u], Gp + u * 32);
+#pragma unroll
+        for (int u = 0; u < RLc; ++u)  // OA, OC, OB, OIB are consecutive slots
+          tpp_cp8_if(r_src[u] != nullptr, col_s + (L::OA + u * 32 + lane) * (LD * 8), r_src[u] + q * r_stride[u]);
+        const double* __restrict__ vp = a.vars + q * STRIDE + lane;  // start state [x|s|y|z]
+#pragma unroll
+        for (int u = 0; u < VLc; ++u)
+          tpp_cp8_if(v_dst[u] != 0, v_dst[u] < 0 ? row_s + (v_dst[u] & 0x7fffffff) : col_s + v_dst[u], vp + u * 32);
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      loading = take;
+    }
+    if (!ASYNC && idle != 0u && next < wend) {
       const int rank = __popc(idle & ((1u << lane) - 1u));
       const bool take = !live && (next + rank < wend);
       if (take) prob = next + rank;
@@ -356,7 +482,6 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
       if (next > wend) next = wend;
       // the lane's own x, y and the guess kernel's verdict first: their latency overlaps the cooperative loads
       double xin[N], yin[KD];
-      int st_in = -1;
       if (take) {
         const double* __restrict__ vp = a.vars + prob * STRIDE;
 #pragma unroll
@@ -455,7 +580,7 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
       __syncwarp();
     }
     if (!__any_sync(FULL, live)) {
-      if (next >= wend) break;
+      if (next >= wend && !__any_sync(FULL, loading)) break;
       continue;
     }
     int done_status = -1;
