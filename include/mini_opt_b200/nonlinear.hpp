@@ -22,6 +22,7 @@
 #include <memory>
 #include <optional>
 #include <utility>
+#include <variant>
 
 #include "mini_opt_b200/qp.hpp"
 
@@ -40,6 +41,26 @@ enum class NLSTerminationState {                                                
   QP_FAILED
 };
 
+// names as the reference's ostream operators print them (structs.cc:50-120)
+inline const char* ToString(OptimizerState s) { return s == OptimizerState::NOMINAL ? "NOMINAL" : "ATTEMPTING_RESTORE_LM"; }
+inline const char* ToString(LineSearchStrategy s) {
+  return s == LineSearchStrategy::ARMIJO_BACKTRACK ? "ARMIJO_BACKTRACK" : "POLYNOMIAL_APPROXIMATION";
+}
+inline const char* ToString(StepSizeSelectionResult s) {
+  static const char* const names[] = {"SUCCESS", "MAX_ITERATIONS", "FIRST_ORDER_SATISFIED", "POSITIVE_DERIVATIVE",
+                                      "FAILURE_NON_FINITE_COST", "FAILURE_INVALID_ALPHA"};
+  return names[static_cast<int>(s)];
+}
+inline const char* ToString(NLSTerminationState s) {
+  static const char* const names[] = {"MAX_ITERATIONS", "SATISFIED_ABSOLUTE_TOL", "SATISFIED_RELATIVE_TOL",
+                                      "SATISFIED_FIRST_ORDER_TOL", "MAX_LAMBDA", "QP_INDEFINITE", "USER_CALLBACK", "QP_FAILED"};
+  return names[static_cast<int>(s)];
+}
+inline std::ostream& operator<<(std::ostream& os, OptimizerState s) { return os << ToString(s); }
+inline std::ostream& operator<<(std::ostream& os, LineSearchStrategy s) { return os << ToString(s); }
+inline std::ostream& operator<<(std::ostream& os, StepSizeSelectionResult s) { return os << ToString(s); }
+inline std::ostream& operator<<(std::ostream& os, NLSTerminationState s) { return os << ToString(s); }
+
 struct Errors {  // structs.hpp:169-186
   double f{0}, equality{0};
   double Total(double penalty) const { return f + penalty * equality; }
@@ -53,7 +74,8 @@ struct DirectionalDerivatives {  // structs.hpp:189-199
 };
 struct LineSearchStep { double alpha; Errors errors; };  // structs.hpp:202-205
 
-// One iteration of the outer loop (NLSIteration, structs.hpp:251-290, without the per-QP-iteration log).
+// One iteration of the outer loop (NLSIteration, structs.hpp:251-290). `qp_outputs` is the reference's variant; its
+// `iterations` vector is filled when Params::record_qp_iterations is set. qp_eigenvalues is never computed (JSON: null).
 struct NLSIteration {
   int iteration;
   OptimizerState optimizer_state;
@@ -65,12 +87,100 @@ struct NLSIteration {
   double penalty;
   StepSizeSelectionResult step_result;
   std::vector<LineSearchStep> line_search_steps;
+  std::variant<QPNullSpaceTerminationState, QPInteriorPointSolverOutputs> qp_outputs{};
+
+  // structs.cc:159-206. ANSI colours as the reference: green 112 / red 160 / orange 202, reset "\x1b[0m".
+  std::string ToString(bool use_color = false, bool include_qp = false) const {
+    using detail::Fmt;
+    using detail::Printf;
+    auto color = [use_color](int code) {
+      return !use_color ? std::string() : (code < 0 ? std::string("\x1b[0m") : "\x1b[38;5;" + std::to_string(code) + "m");
+    };
+    std::string r = "Iteration # " + std::to_string(iteration) + ", state = " + mini_opt_b200::ToString(optimizer_state) +
+                    ", lambda = " + Fmt(lambda) + "\n";
+    r += "  f(0): " + Printf("%.16e", errors_initial.f) + ", c(0): " + Printf("%.16e", errors_initial.equality) +
+         ", total: " + Printf("%.16e", errors_initial.Total(penalty)) + "\n";
+    r += "  penalty = " + Printf("%.16f", penalty) + "\n";
+    const QPInteriorPointSolverOutputs* ip = std::get_if<QPInteriorPointSolverOutputs>(&qp_outputs);
+    if (ip) {
+      r += std::string("  QP-IP: ") + mini_opt_b200::ToString(ip->termination_state) + ", " +
+           std::to_string(ip->iterations.empty() ? static_cast<std::size_t>(ip->num_iterations) : ip->iterations.size()) + "\n";
+    } else {
+      r += std::string("  QP: ") + mini_opt_b200::ToString(std::get<QPNullSpaceTerminationState>(qp_outputs)) + "\n";
+    }
+    r += "  df/dalpha = " + Fmt(directional_derivatives.d_f) + ", dc/dalpha = " + Fmt(directional_derivatives.d_equality) + "\n";
+    r += "  Search result: " + color(step_result == StepSizeSelectionResult::SUCCESS ? 112 : 160) +
+         mini_opt_b200::ToString(step_result) + color(-1) + "\n";
+    std::size_t i = 0;
+    for (const LineSearchStep& step : line_search_steps) {
+      const std::string idx = std::to_string(i++);
+      r += "  f(" + idx + "): " + Printf("%.16e", step.errors.f) + ", c(" + idx + "): " + Printf("%.16e", step.errors.equality) +
+           ", total: " + Printf("%.16e", step.errors.Total(penalty)) + ", alpha = " + Printf("%.10f", step.alpha) + "\n";
+    }
+    if (ip && include_qp)
+      for (const QPInteriorPointIteration& it : ip->iterations) r += it.ToString();
+    return r;
+  }
+  std::string ToJson() const {  // serialization.cc:112-123, keys in nlohmann's alphabetical order
+    using detail::Json;
+    auto errors = [](const Errors& e) { return "{\"equality\":" + Json(e.equality) + ",\"f\":" + Json(e.f) + "}"; };
+    std::string r = "{\"directional_derivatives\":{\"d_equality\":" + Json(directional_derivatives.d_equality) +
+                    ",\"d_f\":" + Json(directional_derivatives.d_f) + "},\"errors_initial\":" + errors(errors_initial) +
+                    ",\"iteration\":" + std::to_string(iteration) + ",\"lambda\":" + Json(lambda) + ",\"line_search_steps\":[";
+    for (std::size_t i = 0; i < line_search_steps.size(); ++i)
+      r += std::string(i ? "," : "") + "{\"alpha\":" + Json(line_search_steps[i].alpha) + ",\"errors\":" +
+           errors(line_search_steps[i].errors) + "}";
+    r += std::string("],\"optimizer_state\":\"") + mini_opt_b200::ToString(optimizer_state) + "\",\"penalty\":" + Json(penalty) +
+         ",\"qp_eigenvalues\":null,\"qp_outputs\":";
+    if (const QPInteriorPointSolverOutputs* ip = std::get_if<QPInteriorPointSolverOutputs>(&qp_outputs)) r += ip->ToJson();
+    else r += std::string("\"") + mini_opt_b200::ToString(std::get<QPNullSpaceTerminationState>(qp_outputs)) + "\"";
+    return r + ",\"step_result\":\"" + mini_opt_b200::ToString(step_result) + "\"}";
+  }
 };
 struct NLSSolverOutputs {  // structs.hpp:293-301
   NLSTerminationState termination_state = NLSTerminationState::MAX_ITERATIONS;
   std::vector<NLSIteration> iterations;
   Vector variables;  // batched API: the final variables travel with the outputs
   int qp_failure_status = 0;  // QP_FAILED: MO_QP_FAILED_FACTORIZATION or MO_QP_NONPOSITIVE_SLACK of the inner solve
+
+  std::size_t NumQPIterations() const {  // structs.cc:208-219: a null-space solve counts as one
+    std::size_t total = 0;
+    for (const NLSIteration& it : iterations) total += static_cast<std::size_t>(it.qp_iterations);
+    return total;
+  }
+  std::size_t NumLineSearchSteps() const {  // structs.cc:221-226
+    std::size_t total = 0;
+    for (const NLSIteration& it : iterations) total += it.line_search_steps.size();
+    return total;
+  }
+  std::size_t NumFailedLineSearches() const {  // structs.cc:228-237
+    std::size_t total = 0;
+    for (const NLSIteration& it : iterations)
+      total += it.step_result != StepSizeSelectionResult::SUCCESS && it.step_result != StepSizeSelectionResult::FIRST_ORDER_SATISFIED;
+    return total;
+  }
+  std::string ToString(bool use_color = false, bool include_qp = false) const {  // structs.cc:239-268
+    std::string r;
+    for (const NLSIteration& it : iterations) r += it.ToString(use_color, include_qp);
+    int code = -1;
+    switch (termination_state) {
+      case NLSTerminationState::SATISFIED_ABSOLUTE_TOL:
+      case NLSTerminationState::SATISFIED_RELATIVE_TOL:
+      case NLSTerminationState::SATISFIED_FIRST_ORDER_TOL: code = 112; break;
+      case NLSTerminationState::MAX_LAMBDA:
+      case NLSTerminationState::MAX_ITERATIONS:
+      case NLSTerminationState::USER_CALLBACK: code = 202; break;
+      case NLSTerminationState::QP_INDEFINITE:
+      case NLSTerminationState::QP_FAILED: code = 160; break;
+    }
+    const std::string on = use_color ? "\x1b[38;5;" + std::to_string(code) + "m" : "", off = use_color ? "\x1b[0m" : "";
+    return r + "  termination = " + on + mini_opt_b200::ToString(termination_state) + off + "\n";
+  }
+  std::string ToJson() const {  // serialization.cc:126-134
+    std::string r = "{\"iterations\":[";
+    for (std::size_t i = 0; i < iterations.size(); ++i) r += (i ? "," : "") + iterations[i].ToJson();
+    return r + "],\"termination_state\":\"" + mini_opt_b200::ToString(termination_state) + "\"}";
+  }
 };
 
 // Type-erased residual (residual.hpp:25-118). `Model<R, P>` wraps a functor
@@ -191,6 +301,9 @@ class ConstrainedNonlinearLeastSquares {
     double lambda_decrease_on_restore{0.8};
     double max_lambda{1.};
     double min_lambda{0.};
+    // batched API only: keep the per-step log of every inner QP solve in NLSIteration::qp_outputs.iterations (the
+    // reference always does; here it costs 112 bytes per Newton step of device-to-host traffic)
+    bool record_qp_iterations{false};
   };
   // nonlinear.hpp:127: x <- x (+) alpha * dx
   using Retraction = std::function<void(Vector& x, const Vector& dx, double alpha)>;
@@ -306,7 +419,7 @@ class ConstrainedNonlinearLeastSquares {
       std::vector<int> ns_status;
       std::vector<Vector> ns_x;
       if (null_space) ns_status = QPNullSpaceSolver::SolveBatch(qps, &ns_x, device);
-      else sol = QPInteriorPointSolver::SolveBatch(qps, qp_params, device);
+      else sol = QPInteriorPointSolver::SolveBatch(qps, qp_params, device, nullptr, params.record_qp_iterations);
       for (std::size_t a = 0; a < active.size(); ++a) {
         const std::size_t i = active[a];
         State& s = st[i];
@@ -375,7 +488,9 @@ class ConstrainedNonlinearLeastSquares {
         const std::optional<NLSTerminationState> maybe_exit =
             UpdateLambdaAndCheckExitConditions(params, step, s.errors_pre, s.penalty, steps, &s.lambda, &s.state, &s.x, &s.cand);
         out[i].iterations.push_back(NLSIteration{iter, old_state, old_lambda, s.errors_pre, q.termination_state,
-                                                 q.num_iterations, dd, s.penalty, step, std::move(steps)});
+                                                 q.num_iterations, dd, s.penalty, step, std::move(steps), {}});
+        if (null_space) out[i].iterations.back().qp_outputs = QPNullSpaceTerminationState::SUCCESS;
+        else out[i].iterations.back().qp_outputs = q;
         if (maybe_exit) {
           out[i].termination_state = *maybe_exit;
           s.done = true;

@@ -5,8 +5,13 @@
 // Eigen::MatrixXd / Eigen::VectorXd gives the drop-in described in INTEGRATION.md.
 #pragma once
 
+#include <charconv>
+#include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <limits>
 #include <optional>
+#include <ostream>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -68,6 +73,57 @@ enum class BarrierStrategy { COMPLEMENTARITY = 0, FIXED_DECREASE = 1, PREDICTOR_
 enum class InitialGuessMethod { NAIVE = 0, SOLVE_EQUALITY_CONSTRAINED = 1, USER_PROVIDED = 2 };          // structs.hpp:34-41
 enum class QPInteriorPointTerminationState { SATISFIED_KKT_TOL = 0, MAX_ITERATIONS = 1 };                // structs.hpp:97-102
 
+// ---- number formatting of the reference's logs ----
+// The reference prints through {fmt} ("{}" = shortest round-trip digits, fixed notation for 1e-4 <= |v| < 1e16, else
+// d.ddde+XX) and serializes through nlohmann::json (same digits, fixed up to 1e15 with a trailing ".0" on integers,
+// NaN / Inf as null). Both are reproduced on top of std::to_chars so that ToString() / ToJson() of the batched results
+// are byte-identical to the reference's on equal values (tests/golden/logging_reference.txt).
+namespace detail {
+inline std::string FormatShortest(double v, bool json) {
+  if (std::isnan(v)) return json ? "null" : (std::signbit(v) ? "-nan" : "nan");
+  if (std::isinf(v)) return json ? "null" : (v < 0 ? "-inf" : "inf");
+  if (v == 0) return std::signbit(v) ? (json ? "-0.0" : "-0") : (json ? "0.0" : "0");
+  char buf[40];
+  const auto res = std::to_chars(buf, buf + sizeof(buf), std::fabs(v), std::chars_format::scientific);
+  std::string digits;
+  int exp10 = 0;
+  {
+    const std::string t(buf, res.ptr);
+    const std::size_t e = t.find('e');
+    for (std::size_t i = 0; i < e; ++i)
+      if (t[i] != '.') digits += t[i];
+    exp10 = std::stoi(t.substr(e + 1));
+  }
+  const int nd = static_cast<int>(digits.size()), point = exp10 + 1;  // value = 0.d1d2... x 10^point
+  std::string out = v < 0 ? "-" : "";
+  const int fixed_max = json ? 15 : 16;
+  if (point > -4 && point <= fixed_max) {
+    if (point <= 0) {
+      out += "0." + std::string(static_cast<std::size_t>(-point), '0') + digits;
+    } else if (nd <= point) {
+      out += digits + std::string(static_cast<std::size_t>(point - nd), '0');
+      if (json) out += ".0";
+    } else {
+      out += digits.substr(0, static_cast<std::size_t>(point)) + "." + digits.substr(static_cast<std::size_t>(point));
+    }
+  } else {
+    out += digits.substr(0, 1);
+    if (nd > 1) out += "." + digits.substr(1);
+    char eb[16];
+    std::snprintf(eb, sizeof(eb), "e%c%02d", exp10 < 0 ? '-' : '+', exp10 < 0 ? -exp10 : exp10);
+    out += eb;
+  }
+  return out;
+}
+inline std::string Fmt(double v) { return FormatShortest(v, false); }
+inline std::string Json(double v) { return FormatShortest(v, true); }
+inline std::string Printf(const char* format, double v) {
+  char buf[400];
+  std::snprintf(buf, sizeof(buf), format, v);
+  return buf;
+}
+}  // namespace detail
+
 struct KKTError {  // structs.hpp:68-78
   double r_dual = 0, r_comp = 0, r_primal_eq = 0, r_primal_ineq = 0;
   double Max() const {
@@ -76,6 +132,57 @@ struct KKTError {  // structs.hpp:68-78
   }
 };
 struct QPLagrangeMultipliers { double min, l_infinity; };  // structs.hpp:105-113
+struct AlphaValues { double primal{1.0}, dual{1.0}; };  // structs.hpp:44-49
+struct IPIterationOutputs {                               // structs.hpp:52-64
+  double mu{0.0};
+  AlphaValues alpha{};
+  AlphaValues alpha_probe{std::numeric_limits<double>::quiet_NaN(), std::numeric_limits<double>::quiet_NaN()};
+  double mu_affine{std::numeric_limits<double>::quiet_NaN()};
+};
+// One Newton step of one problem (structs.hpp:81-94) = one row of mo_qp_out.iter_log.
+struct QPInteriorPointIteration {
+  KKTError kkt_initial{}, kkt_final{};
+  IPIterationOutputs ip_outputs{};
+  static QPInteriorPointIteration FromLogRow(const double* row) {  // MO_QP_ITER_LOG_STRIDE doubles
+    QPInteriorPointIteration it;
+    it.kkt_initial = KKTError{row[0], row[1], row[2], row[3]};
+    it.kkt_final = KKTError{row[4], row[5], row[6], row[7]};
+    it.ip_outputs.mu = row[8];
+    it.ip_outputs.alpha = AlphaValues{row[9], row[10]};
+    it.ip_outputs.alpha_probe = AlphaValues{row[11], row[12]};
+    it.ip_outputs.mu_affine = row[13];
+    return it;
+  }
+  std::string ToString() const {  // structs.cc:122-148
+    using detail::Fmt;
+    std::string r = "Iteration summary: ||kkt|| max: " + Fmt(kkt_initial.Max()) + " --> " + Fmt(kkt_final.Max()) +
+                    ", mu = " + Fmt(ip_outputs.mu) + ", a_p = " + Fmt(ip_outputs.alpha.primal) +
+                    ", a_d = " + Fmt(ip_outputs.alpha.dual) + "\n";
+    if (!std::isnan(ip_outputs.mu_affine))
+      r += " Probe alphas: a_p = " + Fmt(ip_outputs.alpha_probe.primal) + ", a_d = " + Fmt(ip_outputs.alpha_probe.dual) +
+           ", mu_affine = " + Fmt(ip_outputs.mu_affine) + "\n";
+    r += " KKT errors, L2:\n r_dual = " + Fmt(kkt_initial.r_dual) + " --> " + Fmt(kkt_final.r_dual) +
+         "\n r_comp = " + Fmt(kkt_initial.r_comp) + " --> " + Fmt(kkt_final.r_comp) +
+         "\n r_p_eq = " + Fmt(kkt_initial.r_primal_eq) + " --> " + Fmt(kkt_final.r_primal_eq) +
+         "\n r_p_ineq = " + Fmt(kkt_initial.r_primal_ineq) + " --> " + Fmt(kkt_final.r_primal_ineq) + "\n";
+    return r;
+  }
+  std::string ToJson() const {  // serialization.cc:71-74 (keys in nlohmann's alphabetical order)
+    using detail::Json;
+    auto kkt = [](const KKTError& e) {
+      return "{\"r_comp\":" + Json(e.r_comp) + ",\"r_dual\":" + Json(e.r_dual) + ",\"r_primal_eq\":" + Json(e.r_primal_eq) +
+             ",\"r_primal_ineq\":" + Json(e.r_primal_ineq) + "}";
+    };
+    auto alpha = [](const AlphaValues& a) { return "{\"dual\":" + Json(a.dual) + ",\"primal\":" + Json(a.primal) + "}"; };
+    return "{\"ip_outputs\":{\"alpha\":" + alpha(ip_outputs.alpha) + ",\"alpha_probe\":" + alpha(ip_outputs.alpha_probe) +
+           ",\"mu\":" + Json(ip_outputs.mu) + ",\"mu_affine\":" + Json(ip_outputs.mu_affine) + "},\"kkt_final\":" + kkt(kkt_final) +
+           ",\"kkt_initial\":" + kkt(kkt_initial) + "}";
+  }
+};
+inline const char* ToString(QPInteriorPointTerminationState s) {  // structs.cc:26-36
+  return s == QPInteriorPointTerminationState::SATISFIED_KKT_TOL ? "SATISFIED_KKT_TOL" : "MAX_ITERATIONS";
+}
+inline std::ostream& operator<<(std::ostream& os, QPInteriorPointTerminationState s) { return os << ToString(s); }
 
 struct FailedFactorization : std::runtime_error { using std::runtime_error::runtime_error; };  // qp.hpp:331-333
 
@@ -83,6 +190,9 @@ struct FailedFactorization : std::runtime_error { using std::runtime_error::runt
 struct QPInteriorPointSolverOutputs {
   QPInteriorPointTerminationState termination_state = QPInteriorPointTerminationState::MAX_ITERATIONS;
   int num_iterations = 0;      // == iterations.size() of the reference's outputs
+  // the reference's per-step log (structs.hpp:120-122), filled from mo_qp_out.iter_log when the solve was asked to record
+  // it (Solve: always, like the reference; SolveBatch: `record_iterations`, 112 bytes per step come back from the device)
+  std::vector<QPInteriorPointIteration> iterations;
   KKTError kkt_final;          // iterations.back().kkt_final
   std::optional<QPLagrangeMultipliers> lagrange_multipliers;
   int batch_status = MO_QP_MAX_ITERATIONS;  // MO_QP_*: 2 / 3 where the reference would have thrown
@@ -92,6 +202,15 @@ struct QPInteriorPointSolverOutputs {
   double s(int i) const { return variables[n + i]; }
   double y(int i) const { return variables[n + m + i]; }
   double z(int i) const { return variables[n + m + k + i]; }
+  std::string ToJson() const {  // serialization.cc:76-77
+    std::string r = "{\"iterations\":[";
+    for (std::size_t i = 0; i < iterations.size(); ++i) r += (i ? "," : "") + iterations[i].ToJson();
+    r += "],\"lagrange_multipliers\":";
+    r += lagrange_multipliers ? "{\"l_infinity\":" + detail::Json(lagrange_multipliers->l_infinity) + ",\"min\":" +
+                                    detail::Json(lagrange_multipliers->min) + "}"
+                              : std::string("null");
+    return r + ",\"termination_state\":\"" + ToString(termination_state) + "\"}";
+  }
 };
 
 class QPInteriorPointSolver {
@@ -123,7 +242,7 @@ class QPInteriorPointSolver {
     if (!p_) throw std::invalid_argument("Must have a valid problem");
     std::vector<Vector> init;
     if (params.initial_guess_method == InitialGuessMethod::USER_PROVIDED) init.push_back(variables_);
-    std::vector<QPInteriorPointSolverOutputs> out = SolveBatch({*p_}, params, device, init.empty() ? nullptr : &init);
+    std::vector<QPInteriorPointSolverOutputs> out = SolveBatch({*p_}, params, device, init.empty() ? nullptr : &init, true);
     if (out[0].batch_status == MO_QP_FAILED_FACTORIZATION) throw FailedFactorization("Failed to solve self-adjoint system");
     if (out[0].batch_status == MO_QP_NONPOSITIVE_SLACK) throw std::runtime_error("Some slack variables s <= 0");
     variables_ = out[0].variables;
@@ -154,7 +273,8 @@ class QPInteriorPointSolver {
   // (the batched SetVariables) and ignored otherwise.
   static std::vector<QPInteriorPointSolverOutputs> SolveBatch(const std::vector<QP>& qps, const Params& params,
                                                               int device = 0,
-                                                              const std::vector<Vector>* initial_variables = nullptr) {
+                                                              const std::vector<Vector>* initial_variables = nullptr,
+                                                              bool record_iterations = false) {
     std::vector<QPInteriorPointSolverOutputs> result(qps.size());
     if (qps.empty()) return result;
     const bool user_guess = params.initial_guess_method == InitialGuessMethod::USER_PROVIDED;
@@ -165,6 +285,8 @@ class QPInteriorPointSolver {
     std::vector<double> G(B * n * n), c(B * n), A(B * k * n + 1), b(B * k + 1), ia(B * m + 1), ib(B * m + 1);
     std::vector<double> vars(B * stride), kkt(B * 4), lag(B * 2);
     std::vector<std::int32_t> iv(B * m + 1), status(B), iters(B);
+    const std::int64_t log_stride = static_cast<std::int64_t>(params.max_iterations > 0 ? params.max_iterations : 0) * MO_QP_ITER_LOG_STRIDE;
+    std::vector<double> log(record_iterations ? B * log_stride : 0);
     bool box = m == 2 * n;
     for (std::int64_t p = 0; p < B; ++p) {
       const QP& q = qps[p];
@@ -198,7 +320,7 @@ class QPInteriorPointSolver {
     prm.decrease_mu_only_on_small_error = params.decrease_mu_only_on_small_error;
     prm.initial_guess_method = static_cast<int>(params.initial_guess_method);
     prm.initialize_mu_with_complementarity = params.initialize_mu_with_complementarity;
-    mo_qp_out out{vars.data(), status.data(), iters.data(), kkt.data(), lag.data(), nullptr, nullptr};
+    mo_qp_out out{vars.data(), status.data(), iters.data(), kkt.data(), lag.data(), log.empty() ? nullptr : log.data(), nullptr};
     const int rc = mo_qp_ip_solve_batch_host(&batch, &prm, &out, device);
     if (rc == MO_ERR_INVALID_PARAMS) throw std::invalid_argument("invalid QPInteriorPointSolver::Params (qp.cc:76-82)");
     if (rc == MO_ERR_INVALID_ARGUMENT) throw std::invalid_argument("invalid problem");
@@ -209,6 +331,9 @@ class QPInteriorPointSolver {
       o.termination_state = status[p] == MO_QP_SATISFIED_KKT_TOL ? QPInteriorPointTerminationState::SATISFIED_KKT_TOL
                                                                  : QPInteriorPointTerminationState::MAX_ITERATIONS;
       o.num_iterations = iters[p];
+      if (!log.empty())
+        for (int it = 0; it < iters[p]; ++it)
+          o.iterations.push_back(QPInteriorPointIteration::FromLogRow(log.data() + p * log_stride + it * MO_QP_ITER_LOG_STRIDE));
       o.kkt_final = KKTError{kkt[4 * p], kkt[4 * p + 1], kkt[4 * p + 2], kkt[4 * p + 3]};
       if (k > 0) o.lagrange_multipliers = QPLagrangeMultipliers{lag[2 * p], lag[2 * p + 1]};
       o.variables.assign(vars.begin() + p * stride, vars.begin() + (p + 1) * stride);
@@ -233,6 +358,10 @@ class QPInteriorPointSolver {
 };
 
 enum class QPNullSpaceTerminationState { SUCCESS = 0, NOT_POSITIVE_DEFINITE = 1 };  // structs.hpp:137-142
+inline const char* ToString(QPNullSpaceTerminationState s) {                         // structs.cc:38-48
+  return s == QPNullSpaceTerminationState::SUCCESS ? "SUCCESS" : "NOT_POSITIVE_DEFINITE";
+}
+inline std::ostream& operator<<(std::ostream& os, QPNullSpaceTerminationState s) { return os << ToString(s); }
 
 // qp.hpp:304-319: equality-constrained QP by the null-space method (source/qp.cc:679-729); the inequality constraints of
 // the problem are ignored like in the reference. SolveBatch: problems of identical (n, k), one device call.

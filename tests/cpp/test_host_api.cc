@@ -44,6 +44,14 @@ int main(int argc, char** argv) {
   CHECK(out.termination_state == QPInteriorPointTerminationState::SATISFIED_KKT_TOL);
   CHECK(std::fabs(out.x(0) - 4.0) < 1e-6 && std::fabs(solver.variables()[0] - 4.0) < 1e-6);
   CHECK(std::fabs(out.z(0) - 2.0) < 1e-5);  // multiplier of the active bound: G x + c + z = 0 -> z = 2
+  // the per-step log of the reference's outputs (structs.hpp:120-122), from iter_log
+  CHECK(static_cast<int>(out.iterations.size()) == out.num_iterations && out.num_iterations > 0);
+  CHECK(out.iterations.back().kkt_final.Max() == out.kkt_final.Max() && out.kkt_final.Max() < 1e-9);
+  CHECK(out.iterations.front().ip_outputs.mu == 1.0 && std::isnan(out.iterations.front().ip_outputs.mu_affine));
+  for (std::size_t i = 1; i < out.iterations.size(); ++i)  // kkt_initial of a step is evaluated with the new mu, its r_dual is the previous step's
+    CHECK(std::fabs(out.iterations[i].kkt_initial.r_dual - out.iterations[i - 1].kkt_final.r_dual) <= 1e-12 * (1.0 + out.iterations[i].kkt_initial.r_dual));
+  CHECK(out.iterations[0].ToString().rfind("Iteration summary: ||kkt|| max: ", 0) == 0);
+  CHECK(out.ToJson().find("\"termination_state\":\"SATISFIED_KKT_TOL\"") != std::string::npos);
   std::vector<QP> batch;
   for (int i = 0; i < 100; ++i) {
     QP q(2);

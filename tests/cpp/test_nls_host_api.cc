@@ -122,6 +122,23 @@ static void TestInequalityConstrainedRosenbrock() {  // nonlinear_test.cc:463-50
     CHECK(o.termination_state != NLSTerminationState::MAX_ITERATIONS && o.termination_state != NLSTerminationState::MAX_LAMBDA);
     CHECK(std::abs(o.variables[0] - 1.2) < 1e-6 && std::abs(o.variables[1] - 0.5) < 1e-6);
   }
+  // per-step QP logs (NLSIteration::qp_outputs, structs.hpp:262-263) on request: same solve, same counts, printable
+  p.record_qp_iterations = true;
+  const std::vector<NLSSolverOutputs> logged = ConstrainedNonlinearLeastSquares::SolveBatch(problems, p, guesses);
+  for (std::size_t i = 0; i < out.size(); ++i) {
+    CHECK(logged[i].termination_state == out[i].termination_state && logged[i].iterations.size() == out[i].iterations.size());
+    CHECK(logged[i].NumQPIterations() == out[i].NumQPIterations() && logged[i].variables[0] == out[i].variables[0]);
+    std::size_t steps = 0;
+    for (const NLSIteration& it : logged[i].iterations) {
+      const QPInteriorPointSolverOutputs* ip = std::get_if<QPInteriorPointSolverOutputs>(&it.qp_outputs);
+      CHECK(ip != nullptr && static_cast<int>(ip->iterations.size()) == it.qp_iterations);
+      steps += ip->iterations.size();
+    }
+    CHECK(steps == logged[i].NumQPIterations());
+    const std::string text = logged[i].ToString(false, true);
+    CHECK(text.find("  QP-IP: ") != std::string::npos && text.find("Iteration summary: ||kkt|| max: ") != std::string::npos);
+    CHECK(logged[i].ToJson().find("\"kkt_initial\"") != std::string::npos);
+  }
 }
 
 static void TestSphereWithNonlinearEqualityConstraints() {  // nonlinear_test.cc:745-830
