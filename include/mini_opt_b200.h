@@ -351,6 +351,34 @@ int mo_chain_fk_batch(const mo_chain_ik_batch* chain, const double* params, doub
 int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_params* params,
                                 const mo_nls_out* out, int device, void* cuda_stream);
 
+/*
+ * Device-side residual FAMILIES defined by functors: the reference's MakeResidual<R, P>(index, functor)
+ * (include/mini_opt/residual.hpp:121-143) keeps user functors on the host; here a problem class is a struct of two
+ * __device__ functions (mini_opt_b200/csrc/nls_families.cuh) for which the SQP + LM kernel is instantiated, so the whole
+ * ConstrainedNonlinearLeastSquares::Solve loop (source/nonlinear.cc:75-158) runs on the device for every start point of a
+ * batch. Built in: the reference's own test problems (test/nonlinear_test.cc:375-387, 580-594, 721-760).
+ */
+enum { MO_NLS_FAMILY_ROSENBROCK = 0, MO_NLS_FAMILY_HIMMELBLAU = 1, MO_NLS_FAMILY_SPHERE_PRODUCT = 2 };
+
+typedef struct mo_nls_family_batch {
+  int32_t family;          /* MO_NLS_FAMILY_*                                                        */
+  int32_t m;               /* inequality constraints, (var, a, b) triplets shared by the batch        */
+  int64_t batch;
+  const int32_t* ineq_var; /* [m]                                                                    */
+  const double* ineq_a;    /* [m]                                                                    */
+  const double* ineq_b;    /* [m]                                                                    */
+  const double* x0;        /* [batch][n] start points                                                */
+  const double* data;      /* optional [batch][data_stride]: per-problem constants of the functor     */
+  int32_t data_stride;
+  int32_t reserved;
+} mo_nls_family_batch;
+
+/* n, cost rows and equality rows of a family (any output may be NULL). */
+int mo_nls_family_dims(int32_t family, int32_t* n, int32_t* n_cost, int32_t* n_eq);
+/* Device pointers, asynchronous on cuda_stream. mo_nls_out.x is [batch][n of the family]. */
+int mo_nls_solve_family_batch(const mo_nls_family_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
+                              int device, void* cuda_stream);
+
 /* Name of the kernel variant mo_qp_ip_solve_batch would launch for this shape ("warp16", "cta", ...). */
 const char* mo_qp_kernel_variant(int32_t n, int32_t k, int32_t m, int32_t flags);
 

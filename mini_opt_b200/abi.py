@@ -288,6 +288,17 @@ class MoChainIkBatch(C.Structure):
     ]
 
 
+MO_NLS_FAMILY_ROSENBROCK, MO_NLS_FAMILY_HIMMELBLAU, MO_NLS_FAMILY_SPHERE_PRODUCT = 0, 1, 2
+
+
+class MoNlsFamilyBatch(C.Structure):
+    _fields_ = [
+        ("family", C.c_int32), ("m", C.c_int32), ("batch", C.c_int64),
+        ("ineq_var", _dp), ("ineq_a", _dp), ("ineq_b", _dp), ("x0", _dp), ("data", _dp),
+        ("data_stride", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
 class MoNlsOut(C.Structure):
     _fields_ = [("x", _dp), ("termination", _dp), ("iterations", _dp), ("qp_iterations", _dp), ("ls_steps", _dp),
                 ("errors", _dp)]

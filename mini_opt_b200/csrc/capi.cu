@@ -835,6 +835,40 @@ int mo_nls_solve_chain_ik_batch(const mo_chain_ik_batch* problems, const mo_nls_
   return rc;
 }
 
+int mo_nls_family_dims(int32_t family, int32_t* n, int32_t* n_cost, int32_t* n_eq) {
+  int vn = 0, vc = 0, vb = 0, ve = 0;
+  const int rc = mo::nls_family_dims(family, &vn, &vc, &vb, &ve);
+  if (rc) { g_last_error = "unknown residual family"; return rc; }
+  if (n) *n = vn;
+  if (n_cost) *n_cost = vc;
+  if (n_eq) *n_eq = ve;
+  return MO_OK;
+}
+
+int mo_nls_solve_family_batch(const mo_nls_family_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
+                              int device, void* cuda_stream) {
+  MO_TRACE();
+  if (!problems || !params || !out || problems->batch < 0 || problems->m < 0) return MO_ERR_INVALID_ARGUMENT;
+  int n = 0;
+  int rc = mo_nls_family_dims(problems->family, &n, nullptr, nullptr);
+  if (rc) return rc;
+  if (problems->m > 0 && (!problems->ineq_var || !problems->ineq_a || !problems->ineq_b)) return MO_ERR_INVALID_ARGUMENT;
+  if (problems->data && problems->data_stride <= 0) return MO_ERR_INVALID_ARGUMENT;
+  rc = check_nls_params(params);
+  if (rc) return rc;
+  if (problems->batch == 0) return MO_OK;
+  if (!problems->x0 || !out->x || !out->termination || !out->iterations) return MO_ERR_INVALID_ARGUMENT;
+  DeviceInfo dev;
+  rc = device_info(device, &dev);
+  if (rc) return rc;
+  DeviceGuard guard(device);
+  if (!guard.ok) { g_last_error = "cudaSetDevice failed"; return MO_ERR_CUDA; }
+  const mo::NlsLaunchInfo info{dev.sms, (size_t)dev.max_smem_optin};
+  rc = mo::nls_launch_family(problems, params, out, info, static_cast<cudaStream_t>(cuda_stream), &g_last_error);
+  if (rc == MO_OK) g_launches.fetch_add(1);
+  return rc;
+}
+
 }  // extern "C"
 
 #ifdef MO_DM_TRACE

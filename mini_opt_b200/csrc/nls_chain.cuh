@@ -270,7 +270,7 @@ __device__ inline void chain_update(ChainWork& C, const double* params) {
 }
 
 // mo_chain_fk_batch: one warp per parameter vector.
-__global__ void __launch_bounds__(32) chain_fk_kernel(const ChainArgs a, const double* __restrict__ params,
+static __global__ void __launch_bounds__(32) chain_fk_kernel(const ChainArgs a, const double* __restrict__ params,
                                                       double* __restrict__ translation, double* __restrict__ rotation_q,
                                                       double* __restrict__ tD, double* __restrict__ rD) {
   extern __shared__ double smem[];
@@ -353,7 +353,7 @@ struct LinearizeArgs {
 };
 
 // mo_nls_linearize_batch: one warp per problem, 4 warps per block.
-__global__ void __launch_bounds__(32) nls_linearize_kernel(const LinearizeArgs a) {
+static __global__ void __launch_bounds__(32) nls_linearize_kernel(const LinearizeArgs a) {
   const int n = a.n, k = a.r_eq, m = a.m;
   for (long long p = blockIdx.x; p < a.batch; p += gridDim.x) {
     linearize_warp(n, a.r_cost, a.cost_block, k, m, a.x + p * n, a.J_cost + p * a.r_cost * n, a.r_cost_v + p * a.r_cost,
@@ -389,11 +389,40 @@ __device__ inline void chain_rows(ChainWork& C, const double* x, int rows, const
   __syncwarp();
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Residual FAMILY: what the SQP kernel needs from a problem class (the device-side counterpart of the reference's
+// type-erased Residual, include/mini_opt/residual.hpp:25-143). A family is a struct with
+//   Args   POD kernel argument with at least { n, n_cost, cost_block, n_eq, m, batch, ineq_var, ineq_a, ineq_b, x0 }
+//   Work   per-warp working state (pointers into the warp's shared-memory region)
+//   smem_doubles(args), carve(work, q, args) -> q', setup(work, args)   once per warp
+//   begin(work, args, p)                                              a new problem starts in this warp
+//   cost_rows / eq_rows(work, args, p, x, r, J)    residual rows at x (and the column-major rows x n Jacobian unless
+//                                                  J == nullptr), written to shared memory, warp-synchronous
+// ChainFamily is the transform-chain IK family; nls_families.cuh adds functor-defined families.
+// ---------------------------------------------------------------------------------------------------------
+struct ChainFamily {
+  using Args = ChainArgs;
+  using Work = ChainWork;
+  __host__ __device__ static size_t smem_doubles(const Args& a) { return chain_smem_doubles(a.links, a.n); }
+  __device__ static double* carve(Work& C, double* q, const Args& a) { return chain_carve(C, q, a.links, a.n); }
+  __device__ static void setup(Work& C, const Args& a) { chain_setup(C, a); }
+  __device__ static void begin(Work& C, const Args&, long long) {
+    if ((threadIdx.x & 31) == 0) *C.have_cache = 0;
+  }
+  __device__ static void cost_rows(Work& C, const Args& a, long long p, const double* x, double* r, double* J) {
+    chain_rows(C, x, a.n_cost, a.cost_w, a.cost_target + p * a.n_cost, r, J);
+  }
+  __device__ static void eq_rows(Work& C, const Args& a, long long p, const double* x, double* r, double* J) {
+    chain_rows(C, x, a.n_eq, a.eq_w, a.eq_target + p * a.n_eq, r, J);
+  }
+};
+
 // EvaluateNonlinearErrors (nonlinear.cc:279-293): every lane returns {f, equality}
-__device__ inline void chain_errors(ChainWork& C, const ChainArgs& a, long long p, const double* x, double* rbuf,
-                                    double& f, double& eq) {
+template <class F>
+__device__ inline void family_errors(typename F::Work& C, const typename F::Args& a, long long p, const double* x,
+                                     double* rbuf, double& f, double& eq) {
   const int cb = a.cost_block > 0 ? a.cost_block : a.n_cost;
-  chain_rows(C, x, a.n_cost, a.cost_w, a.cost_target + p * a.n_cost, rbuf, nullptr);
+  F::cost_rows(C, a, p, x, rbuf, nullptr);
   f = 0.0;
   for (int r0 = 0; r0 < a.n_cost; r0 += cb) {
     double s = 0.0;
@@ -403,17 +432,17 @@ __device__ inline void chain_errors(ChainWork& C, const ChainArgs& a, long long 
   eq = 0.0;
   __syncwarp();
   if (a.n_eq) {
-    chain_rows(C, x, a.n_eq, a.eq_w, a.eq_target + p * a.n_eq, rbuf, nullptr);
+    F::eq_rows(C, a, p, x, rbuf, nullptr);
     for (int i = 0; i < a.n_eq; ++i) eq += fabs(rbuf[i]);
     __syncwarp();
   }
 }
 
-__host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost, int k, int m) {
+__host__ __device__ inline size_t nls_smem_doubles(size_t family_doubles, int n, int n_cost, int k, int m) {
   // inner QP workspace: the interior point solver's, or (equalities and no inequalities) the null-space solver's
   const size_t qpw = (m == 0 && k > 0 && ns_smem_doubles(n, k) > gen_smem_doubles(n, k, m, 32)) ? ns_smem_doubles(n, k)
                                                                                                : gen_smem_doubles(n, k, m, 32);
-  size_t d = chain_smem_doubles(links, n) + qpw;
+  size_t d = family_doubles + qpw;
   d += (size_t)n * n + n + (size_t)k * n + k + m;       // QP: G, c, A, b, shifted bounds
   d += (size_t)n_cost * n + (size_t)k * n + 3 * (size_t)n; // Jc, Je, x, cand, dx
   d += 2 * kMaxChainRows + 8;                            // residual buffers, errors
@@ -426,7 +455,7 @@ __host__ __device__ inline size_t nls_smem_doubles(int links, int n, int n_cost,
 // Problems are handed out through a global ticket counter (zeroed on the launch stream): SQP iteration counts are heavy-tailed
 // (a few % of the IK problems run to max_iterations), a static stride leaves most warps idle while the unlucky ones finish.
 constexpr int kIkTicketSlots = 64;  // launches in flight that may hold a ticket counter at the same time
-__device__ unsigned long long g_ik_tickets[kIkTicketSlots];
+static __device__ unsigned long long g_ik_tickets[kIkTicketSlots];  // one ring per translation unit
 
 // LOCK-STEP schedule: W warps per CTA, each warp owns one problem at a time (ticket queue), and the warps of a CTA walk the
 // phases of an SQP iteration TOGETHER: [fetch] | linearize (FK + Jacobians + J'J) | inner QP | derivatives + line search +
@@ -437,14 +466,14 @@ __device__ unsigned long long g_ik_tickets[kIkTicketSlots];
 // the QP, line search evaluations) have bodies that fit the cache once nobody else is evicting them. The arithmetic of a
 // problem is untouched: results are bit-identical to the W = 1 schedule. Cost: warps idle at the barriers while the slowest
 // QP / line search of the CTA finishes.
-template <int W, int MINB>
-__global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainArgs a, const NlsParams prm, const NlsOut out,
-                                                                    unsigned long long* __restrict__ ticket,
-                                                                    const long long per_warp_doubles, const int sync_mask) {
+template <class F, int W, int MINB>
+__global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename F::Args a, const NlsParams prm, const NlsOut out,
+                                                                 unsigned long long* __restrict__ ticket,
+                                                                 const long long per_warp_doubles, const int sync_mask) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n = a.n, k = a.n_eq, m = a.m;
-  ChainWork C;
-  double* q = chain_carve(C, smem + (long long)warp * per_warp_doubles, a.links, n);
+  typename F::Work C;
+  double* q = F::carve(C, smem + (long long)warp * per_warp_doubles, a);
   GenWork W_;
   gen_carve(W_, q, n, k, m, 32);
   const bool null_space = m == 0 && k > 0;  // solver choice of the reference, nonlinear.cc:83-89
@@ -462,7 +491,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
   double* rc = q; q += kMaxChainRows;
   double* re = q; q += kMaxChainRows;
   double* err = q; q += 8;
-  chain_setup(C, a);
+  F::setup(C, a);
   for (int i = lane; i < m; i += 32) { W_.cv[i] = a.ineq_var[i]; W_.ca[i] = a.ineq_a[i]; }
   __syncwarp();
   GenProb Q{G, cvec, k ? A : nullptr, k ? bvec : nullptr};
@@ -479,7 +508,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
     __syncwarp();
     for (int i = lane; i < n; i += 32) out.x[p * n + i] = x[i];
     double ff = 0.0, fe = 0.0;
-    if (out.errors) chain_errors(C, a, p, x, rc, ff, fe);
+    if (out.errors) family_errors<F>(C, a, p, x, rc, ff, fe);
     if (lane == 0) {
       out.termination[p] = term;
       out.iterations[p] = iters;
@@ -497,7 +526,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
       if (lane == 0) t = atomicAdd(ticket, 1ULL);
       p = (long long)__shfl_sync(0xffffffffu, t, 0);
       if (p >= a.batch) { drained = true; break; }
-      if (lane == 0) *C.have_cache = 0;
+      F::begin(C, a, p);
       for (int i = lane; i < n; i += 32) x[i] = a.x0[p * n + i];
       __syncwarp();
       state = 0; term = MO_NLS_MAX_ITERATIONS; iters = 0; qp_total = 0; ls_total = 0; iter = 0;
@@ -511,8 +540,8 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
     double pre_f = 0.0, pre_eq = 0.0;
     // ---- phase A: LinearizeAndFillQP (nonlinear.cc:170-214) ----
     if (busy) {
-      chain_rows(C, x, a.n_cost, a.cost_w, a.cost_target + p * a.n_cost, rc, Jc);
-      if (k) chain_rows(C, x, k, a.eq_w, a.eq_target + p * k, re, Je);
+      F::cost_rows(C, a, p, x, rc, Jc);
+      if (k) F::eq_rows(C, a, p, x, re, Je);
       linearize_warp(n, a.n_cost, a.cost_block, k, m, x, Jc, rc, Je, re, lambda, a.ineq_var, a.ineq_a, a.ineq_b, G, cvec,
                      A, bvec, W_.cb, err);
       pre_f = err[0]; pre_eq = err[1];
@@ -606,7 +635,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
           cand[i] = prm.retraction == MO_RETRACT_MOD_PI ? mod_pi(v) : v;
         }
         __syncwarp();
-        chain_errors(C, a, p, cand, rc, last_f, last_eq);
+        family_errors<F>(C, a, p, cand, rc, last_f, last_eq);
         a_prev2 = a_prev; phi_prev2 = phi_prev;
         a_prev = alpha; phi_prev = last_f + penalty * last_eq;
         ++ls_total;
@@ -640,5 +669,8 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_chain_ik_kernel(const ChainA
     if (busy && ended) finish();
   }
 }
+
+template <int W, int MINB>
+constexpr auto nls_chain_ik_kernel = nls_solve_kernel<ChainFamily, W, MINB>;
 
 }  // namespace mo

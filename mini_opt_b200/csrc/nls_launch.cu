@@ -1,9 +1,8 @@
 // Launchers of the nonlinear least squares kernels (nls_chain.cuh, nls_linearize_dmma.cuh). Called from capi.cu.
 #include <atomic>
 
-#include "nls_chain.cuh"
+#include "nls_solve_launch.cuh"
 #include "nls_linearize_dmma.cuh"
-#include "nls_launch.h"
 
 namespace mo {
 namespace {
@@ -17,16 +16,6 @@ std::atomic<int> g_ik_warps{MO_IK_WARPS};  // mo_debug_set_ik_warps
 #endif
 std::atomic<int> g_ik_sync{MO_IK_SYNC};    // mo_debug_set_ik_sync: CTA barriers after phase A (1) and phase B (2)
 
-int cuda_err(cudaError_t e, const char* what, std::string* err) {
-  *err = std::string(what) + ": " + cudaGetErrorString(e);
-  return MO_ERR_CUDA;
-}
-#define NLS_CUDA(call)                                          \
-  do {                                                          \
-    cudaError_t e_ = (call);                                    \
-    if (e_ != cudaSuccess) return cuda_err(e_, #call, err);     \
-  } while (0)
-
 ChainArgs make_chain_args(const mo_chain_ik_batch* b) {
   ChainArgs a{};
   a.links = b->links; a.n = b->n; a.n_cost = b->n_cost; a.cost_block = b->cost_block; a.n_eq = b->n_eq; a.m = b->m;
@@ -34,20 +23,6 @@ ChainArgs make_chain_args(const mo_chain_ik_batch* b) {
   a.cost_target = b->cost_target; a.eq_w = b->eq_w; a.eq_target = b->eq_target; a.ineq_var = b->ineq_var;
   a.ineq_a = b->ineq_a; a.ineq_b = b->ineq_b; a.x0 = b->x0;
   return a;
-}
-
-template <typename K>
-int block_grid(K kernel, int threads, size_t smem, long long blocks_wanted, const NlsLaunchInfo& dev, int* grid, std::string* err) {
-  if (smem > dev.max_smem_optin) {
-    *err = "problem too large for shared memory: needs " + std::to_string(smem) + " bytes";
-    return MO_ERR_UNSUPPORTED_SHAPE;
-  }
-  int bps = 0;
-  NLS_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  NLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, threads, smem));
-  const long long cap = (long long)dev.sms * (bps > 0 ? bps : 1);
-  *grid = (int)(blocks_wanted < cap ? blocks_wanted : cap);
-  return MO_OK;
 }
 
 }  // namespace
@@ -87,7 +62,7 @@ int nls_launch_chain_fk(const mo_chain_ik_batch* chain, const double* params, do
                         std::string* err) {
   const size_t smem = sizeof(double) * chain_smem_doubles(chain->links, chain->n);
   int grid = 0;
-  const int rc = block_grid(chain_fk_kernel, 32, smem, chain->batch, dev, &grid, err);
+  const int rc = nls_block_grid(chain_fk_kernel, 32, smem, chain->batch, dev, &grid, err);
   if (rc) return rc;
   chain_fk_kernel<<<grid, 32, smem, stream>>>(make_chain_args(chain), params, translation, rotation_q, t_D_params, r_D_params);
   NLS_CUDA(cudaGetLastError());
@@ -96,39 +71,16 @@ int nls_launch_chain_fk(const mo_chain_ik_batch* chain, const double* params, do
 
 int nls_launch_chain_ik(const mo_chain_ik_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
                         const NlsLaunchInfo& dev, cudaStream_t stream, std::string* err) {
-  const NlsParams p{params->max_iterations, params->max_qp_iterations, params->termination_kkt_tolerance,
-                    params->absolute_exit_tol, params->relative_exit_tol, params->absolute_first_derivative_tol,
-                    params->max_line_search_iterations, params->line_search_strategy, params->armijo_search_tau,
-                    params->equality_penalty_initial, params->equality_penalty_scale_factor,
-                    params->equality_penalty_rho, params->lambda_initial, params->lambda_failure_init,
-                    params->lambda_decrease_on_success, params->lambda_decrease_on_restore, params->max_lambda,
-                    params->min_lambda, params->retraction, params->inner_qp_solver};
-  const NlsOut o{out->x, out->termination, out->iterations, out->qp_iterations, out->ls_steps, out->errors};
-  // ticket counter of this launch: a slot of a small ring in device memory, zeroed on the launch stream
-  static std::atomic<unsigned> ring{0};
-  unsigned long long* tickets = nullptr;
-  NLS_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&tickets), g_ik_tickets));
-  tickets += ring.fetch_add(1) % kIkTicketSlots;
-  NLS_CUDA(cudaMemsetAsync(tickets, 0, sizeof(unsigned long long), stream));
-  const long long per_warp = (long long)((nls_smem_doubles(problems->links, problems->n, problems->n_cost, problems->n_eq, problems->m) + 1) & ~size_t(1));
   const ChainArgs ca = make_chain_args(problems);
-  auto launch = [&](auto kernel, int warps) -> int {
-    const size_t smem = sizeof(double) * (size_t)per_warp * warps;
-    int grid = 0;
-    const int rc = block_grid(kernel, 32 * warps, smem, (problems->batch + warps - 1) / warps, dev, &grid, err);
-    if (rc) return rc;
-    kernel<<<grid, 32 * warps, smem, stream>>>(ca, p, o, tickets, per_warp, g_ik_sync.load());
-    NLS_CUDA(cudaGetLastError());
-    return MO_OK;
-  };
+  const int mask = g_ik_sync.load();
   // warps per CTA marching in lock-step (nls_chain.cuh); W x MINB = 16 resident warps per SM as measured best in round 1
   int w = g_ik_warps.load();
-  while (w > 1 && sizeof(double) * (size_t)per_warp * w > dev.max_smem_optin) w /= 2;
+  while (w > 1 && sizeof(double) * (size_t)nls_per_warp_doubles<ChainFamily>(ca) * w > dev.max_smem_optin) w /= 2;
   switch (w) {
-    case 16: return launch(nls_chain_ik_kernel<16, 1>, 16);
-    case 8: return launch(nls_chain_ik_kernel<8, 2>, 8);
-    case 4: return launch(nls_chain_ik_kernel<4, 4>, 4);
-    default: return launch(nls_chain_ik_kernel<1, 16>, 1);
+    case 16: return nls_solve_launch<ChainFamily, 16, 1>(ca, params, out, dev, stream, mask, err);
+    case 8: return nls_solve_launch<ChainFamily, 8, 2>(ca, params, out, dev, stream, mask, err);
+    case 4: return nls_solve_launch<ChainFamily, 4, 4>(ca, params, out, dev, stream, mask, err);
+    default: return nls_solve_launch<ChainFamily, 1, 16>(ca, params, out, dev, stream, mask, err);
   }
 }
 

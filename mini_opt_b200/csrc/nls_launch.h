@@ -27,4 +27,9 @@ int nls_launch_chain_fk(const mo_chain_ik_batch* chain, const double* params, do
 int nls_launch_chain_ik(const mo_chain_ik_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
                         const NlsLaunchInfo& dev, cudaStream_t stream, std::string* err);
 
+// functor residual families (nls_families.cu)
+int nls_family_dims(int family, int* n, int* n_cost, int* cost_block, int* n_eq);
+int nls_launch_family(const mo_nls_family_batch* problems, const mo_nls_params* params, const mo_nls_out* out,
+                      const NlsLaunchInfo& dev, cudaStream_t stream, std::string* err);
+
 }  // namespace mo

@@ -46,6 +46,26 @@ def solve_chain_ik_device(ch: abi.ChainIKArrays, params: abi.NLSParams, out: abi
                                                      st.cuda_stream))
 
 
+def family_dims(family: int):
+    """(n, cost rows, equality rows) of a functor residual family (``mo_nls_family_dims``)."""
+    n, rc, re = C.c_int32(), C.c_int32(), C.c_int32()
+    lib.check(lib.load().mo_nls_family_dims(family, C.byref(n), C.byref(rc), C.byref(re)))
+    return n.value, rc.value, re.value
+
+
+def solve_family_device(family: int, x0, params: abi.NLSParams, out: abi.NLSOutArrays, device, ineq=None, data=None,
+                        stream=None):
+    """``mo_nls_solve_family_batch`` on device tensors: ``x0`` [batch, n]; ``ineq`` = (var int32 [m], a [m], b [m]) device
+    tensors shared by the batch; ``data`` optional [batch, stride] per-problem constants of the functor."""
+    import torch
+    st = stream if stream is not None else torch.cuda.current_stream(device)
+    var, a, b = ineq if ineq is not None else (None, None, None)
+    c = abi.MoNlsFamilyBatch(family, 0 if var is None else int(var.numel()), int(x0.shape[0]), abi._addr(var), abi._addr(a),
+                             abi._addr(b), abi._addr(x0), abi._addr(data), 0 if data is None else int(data.shape[1]), 0)
+    p, o = params.to_c(), out.to_c()
+    lib.check(lib.load().mo_nls_solve_family_batch(C.byref(c), C.byref(p), C.byref(o), _device_index(device), st.cuda_stream))
+
+
 _CHAIN_ARRAYS = ("link_pose", "link_mask", "cost_w", "cost_target", "eq_w", "eq_target", "ineq_var", "ineq_a", "ineq_b", "x0")
 
 

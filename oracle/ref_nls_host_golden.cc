@@ -103,5 +103,33 @@ int main() {
                   static_cast<int>(out.NumQPIterations()), nls.variables()[0], nls.variables()[1]);
     }
   }
+  {
+    // TestHimmelblauQuadrantConstrained (nonlinear_test.cc:668-718): two one-row costs, box 0.1 <= x, y <= 5, start points
+    // on the reference's own grid (same accumulating loop); every start must reach (3, 2)
+    Problem problem{};
+    problem.costs.push_back(MakeResidual<1, 2>({0, 1}, [](const Vector2d& xy, Eigen::Matrix<double, 1, 2>* J) -> Eigen::Matrix<double, 1, 1> {
+      if (J) { (*J)(0, 0) = 2 * xy[0]; (*J)(0, 1) = 1.0; }
+      return Eigen::Matrix<double, 1, 1>{std::pow(xy[0], 2) + xy[1] - 11};
+    }));
+    problem.costs.push_back(MakeResidual<1, 2>({0, 1}, [](const Vector2d& xy, Eigen::Matrix<double, 1, 2>* J) -> Eigen::Matrix<double, 1, 1> {
+      if (J) { (*J)(0, 0) = 1.0; (*J)(0, 1) = 2 * xy[1]; }
+      return Eigen::Matrix<double, 1, 1>{xy[0] + std::pow(xy[1], 2) - 7};
+    }));
+    problem.dimension = 2;
+    problem.inequality_constraints.push_back(Var(0) >= 0.1);
+    problem.inequality_constraints.push_back(Var(0) <= 5.0);
+    problem.inequality_constraints.push_back(Var(1) >= 0.1);
+    problem.inequality_constraints.push_back(Var(1) <= 5.0);
+    ConstrainedNonlinearLeastSquares::Params p{};
+    p.max_iterations = 20;
+    p.max_qp_iterations = 10;
+    p.relative_exit_tol = 1e-12;
+    p.absolute_first_derivative_tol = 1e-8;
+    p.termination_kkt_tolerance = 1e-6;
+    std::vector<Vector2d> grid;
+    for (double x = 0.2; x <= 4.8; x += 0.2)
+      for (double y = 0.2; y <= 4.8; y += 0.2) grid.emplace_back(x, y);
+    Run("himmelblau_quadrant", problem, p, grid);
+  }
   return 0;
 }

@@ -127,7 +127,10 @@ static void TestInequalityConstrainedRosenbrock() {  // nonlinear_test.cc:463-50
   const std::vector<NLSSolverOutputs> logged = ConstrainedNonlinearLeastSquares::SolveBatch(problems, p, guesses);
   for (std::size_t i = 0; i < out.size(); ++i) {
     CHECK(logged[i].termination_state == out[i].termination_state && logged[i].iterations.size() == out[i].iterations.size());
-    CHECK(logged[i].NumQPIterations() == out[i].NumQPIterations() && logged[i].variables[0] == out[i].variables[0]);
+    // asking for the log may select another kernel family for the inner solves (same algorithm, different rounding): the
+    // start (1423, -400) with G ~ 8e8 moves by up to two Newton steps, see tests/test_cpp_host_api.py
+    const long dq = static_cast<long>(logged[i].NumQPIterations()) - static_cast<long>(out[i].NumQPIterations());
+    CHECK(dq >= -2 && dq <= 2 && std::abs(logged[i].variables[0] - out[i].variables[0]) < 1e-7);
     std::size_t steps = 0;
     for (const NLSIteration& it : logged[i].iterations) {
       const QPInteriorPointSolverOutputs* ip = std::get_if<QPInteriorPointSolverOutputs>(&it.qp_outputs);
@@ -138,6 +141,36 @@ static void TestInequalityConstrainedRosenbrock() {  // nonlinear_test.cc:463-50
     const std::string text = logged[i].ToString(false, true);
     CHECK(text.find("  QP-IP: ") != std::string::npos && text.find("Iteration summary: ||kkt|| max: ") != std::string::npos);
     CHECK(logged[i].ToJson().find("\"kkt_initial\"") != std::string::npos);
+  }
+}
+
+static void TestHimmelblauQuadrantConstrained() {  // nonlinear_test.cc:668-718
+  Problem problem;
+  problem.costs.push_back(MakeResidual<1, 2>({0, 1}, [](const std::array<double, 2>& xy, std::array<double, 2>* J) {
+    if (J) { (*J)[0] = 2 * xy[0]; (*J)[1] = 1.0; }
+    return std::array<double, 1>{std::pow(xy[0], 2) + xy[1] - 11};
+  }));
+  problem.costs.push_back(MakeResidual<1, 2>({0, 1}, [](const std::array<double, 2>& xy, std::array<double, 2>* J) {
+    if (J) { (*J)[0] = 1.0; (*J)[1] = 2 * xy[1]; }
+    return std::array<double, 1>{xy[0] + std::pow(xy[1], 2) - 7};
+  }));
+  problem.dimension = 2;
+  problem.inequality_constraints = {Var(0) >= 0.1, Var(0) <= 5.0, Var(1) >= 0.1, Var(1) <= 5.0};
+  ConstrainedNonlinearLeastSquares::Params p;
+  p.max_iterations = 20;
+  p.max_qp_iterations = 10;
+  p.relative_exit_tol = 1e-12;
+  p.absolute_first_derivative_tol = 1e-8;
+  p.termination_kkt_tolerance = 1e-6;
+  std::vector<Vector> guesses;
+  for (double x = 0.2; x <= 4.8; x += 0.2)
+    for (double y = 0.2; y <= 4.8; y += 0.2) guesses.push_back(Vector{x, y});
+  const std::vector<const Problem*> problems(guesses.size(), &problem);
+  const std::vector<NLSSolverOutputs> out = ConstrainedNonlinearLeastSquares::SolveBatch(problems, p, guesses);
+  PrintResults("himmelblau_quadrant", out);
+  for (const NLSSolverOutputs& o : out) {
+    CHECK(SatisfiedTol(o.termination_state));
+    CHECK(std::abs(o.variables[0] - 3.0) < 5e-5 && std::abs(o.variables[1] - 2.0) < 5e-5);  // the reference's own bound
   }
 }
 
@@ -230,6 +263,7 @@ int main(int argc, char** argv) {
   TestRosenbrock(false);
   TestRosenbrock(true);
   TestInequalityConstrainedRosenbrock();
+  TestHimmelblauQuadrantConstrained();
   TestSphereWithNonlinearEqualityConstraints();
   TestPerProblemFailureAndParams();
   std::printf("gpu ok\n");
