@@ -116,7 +116,8 @@ def test_himmelblau_quadrant_on_device():
     o = solve(abi.MO_NLS_FAMILY_HIMMELBLAU, starts, p, ineq=([0, 0, 1, 1], [1.0, -1.0, 1.0, -1.0], [-0.1, 5.0, -0.1, 5.0]))
     got = {("himmelblau_quadrant", i): v for i, v in rows(o).items()}
     ref = {("himmelblau_quadrant", i): v for i, v in golden("himmelblau_quadrant").items()}
-    compare_himmelblau(got, ref, tag="device")
+    # measured on B200 (round 2): 529 / 529 identical termination, outer and QP iteration counts
+    compare_himmelblau(got, ref, floors={"termination": 0.995, "termination_and_outer": 0.995, "all_counts": 0.995}, tag="device")
 
 
 class MT19937:
