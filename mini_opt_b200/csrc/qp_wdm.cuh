@@ -92,6 +92,24 @@ __device__ __forceinline__ double wd_sum_r(double v) {
   return v;
 }
 
+// LOCK-STEP CTAs (LOCK > 1): LOCK warps per CTA, each with its own problem in its own shared-memory region, walk the block
+// columns of their factorizations TOGETHER -- a CTA barrier before and after every diagonal block -- so that an SM is either
+// in a DMMA phase (panel solve of column J + gather of column J+1, all warps) or in a pivot-chain phase (diagonal block J,
+// all warps). Why: DMMA.8x8x4 holds the FP64 pipe of a sub-partition for 16 cycles; with the phases of the resident warps
+// interleaved at random every dependent DFMA of a pivot chain queues behind other warps' DMMAs (16-25 cycles per dependent
+// operation instead of 8, profiles/r02_lanes_microbench.txt), and the chain is 37 % of the kernel
+// (profiles/r02_wd64_phase_trace.txt). The barriers order nothing -- no data is shared between the warps.
+// MEASURED (profiles/r02_wd_lockstep_ab.txt): the hypothesis is wrong for this kernel. With every warp of the SM in its
+// pivot-chain phase at once the diagonal blocks take exactly as long (1.60M cycles of a 4.4M-cycle launch either way): the
+// block costs ~430 issued instructions at ~3.7 cycles each, not queueing behind DMMAs; the barriers only add waiting
+// (n=64 19.2 vs 18.7 ms, n=32 23.5 vs 18.2, n=16 25.9 vs 18.5). Off by default, kept behind mo_debug_set_wd_lock.
+template <int LOCK>
+__device__ __forceinline__ void wd_lock_bar() {
+  if constexpr (LOCK > 1) __syncthreads();
+}
+template <int N, int K>
+__host__ __device__ constexpr int wd_lock_barriers() { return 2 * WdLayout<N, K>::NT; }  // per factorization, after the opening __syncthreads_or
+
 // cp.async staging of G (lower block triangle) and A_eq into the tiles; every request is 8 rows x 4 columns:
 // four 64-byte column segments in global memory, 256 contiguous bytes in shared memory.
 template <int N, int K, int NW>
@@ -232,7 +250,7 @@ __device__ __forceinline__ void wd_forward_block(double* __restrict__ sm, int la
 // Block column J of the left-looking factorization: gather the updates of all earlier panels into the accumulator
 // fragments of tiles (J..NT, J), factor the diagonal block, solve the panel (and the right-hand-side row) with DMMA
 // against T = inv(L_JJ)' D_J^-1.
-template <int N, int K, int J>
+template <int N, int K, int J, int LOCK = 1>
 __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, double& chk) {
   using L = WdLayout<N, K>;
   constexpr int CNT = L::NTR - J;
@@ -266,9 +284,11 @@ __device__ __forceinline__ void wd_column(double* __restrict__ sm, int lane, dou
   for (int i = 0; i < CNT; ++i)
     *reinterpret_cast<double2*>(T + L::tile(J + i, J) + coff) = make_double2(acc[i][0], acc[i][1]);
   __syncwarp();
+  wd_lock_bar<LOCK>();  // DMMA phase of the CTA ends
   WD_T(2);
   wd_diag_block(T + L::tile(J, J), sm + L::O_D + 8 * J, sm + L::O_INVD + 8 * J, chk);
   if constexpr (!L::RHS_ROW) wd_forward_block<N, K, J>(sm, lane);
+  wd_lock_bar<LOCK>();  // pivot-chain phase ends
   WD_T(3);
   const double idr = sm[L::O_INVD + 8 * J + r];
   const double bt0 = T[L::tile(J, J) + lane] * idr, bt1 = T[L::tile(J, J) + 32 + (lane ^ 8)] * idr;
@@ -561,27 +581,28 @@ __device__ __forceinline__ void wdl_columns(double* __restrict__ sm, int lane, d
   }
 }
 
-template <int N, int K, int NW, int J>
+template <int N, int K, int NW, int J, int LOCK = 1>
 __device__ __forceinline__ void wd_columns(double* __restrict__ sm, int lane, int warp, double& chk) {
   if constexpr (J < WdLayout<N, K>::NT) {
-    if constexpr (NW == 1) wd_column<N, K, J>(sm, lane, chk);
+    if constexpr (NW == 1) wd_column<N, K, J, LOCK>(sm, lane, chk);
     else wd2_column<N, K, J>(sm, lane, warp, chk);
-    wd_columns<N, K, NW, J + 1>(sm, lane, warp, chk);
+    wd_columns<N, K, NW, J + 1, LOCK>(sm, lane, warp, chk);
   }
 }
 
 // Factor the KKT matrix held in the tiles and solve for the right-hand side held in row 0 of tile row NT.
 // On return sm[O_XV .. O_XV + P) = K^-1 rhs and the cp.async staging of G, A_eq for the next trip is in flight. Returns false on a zero or non-finite pivot (-> MO_QP_FAILED_FACTORIZATION,
 // the batched stand-in for the exception of qp.cc:303-307); with two warps only warp 0 holds the answer.
-template <int N, int K, int NW, bool LA, bool PBS>
+template <int N, int K, int NW, bool LA, bool PBS, int LOCK = 1>
 __device__ __forceinline__ bool wd_factor_solve(double* __restrict__ sm, int lane, int warp,
                                                 const double* __restrict__ Gp, const double* __restrict__ Ap) {
   using L = WdLayout<N, K>;
   constexpr bool kStageInBacksub = WdLayout<N, K>::STAGE_IN_BACKSUB;
   double chk = 0.0;
+  if constexpr (LOCK > 1) __syncthreads_or(1);  // the factorizations of the CTA's warps start together (see the kernel's tail)
   WD_T(1);
   if constexpr (LA) wdl_columns<N, K, 0>(sm, lane, chk);
-  else wd_columns<N, K, NW, 0>(sm, lane, warp, chk);
+  else wd_columns<N, K, NW, 0, LOCK>(sm, lane, warp, chk);
   if constexpr (LA) WD_T(3);
   if (NW == 2 && warp != 0) return true;
   // back substitution L' x = w, w = D^-1 L^-1 rhs = row 0 of tile row NT; block J: t = w_J - sum_{I > J} L(I,J)' x_I,
@@ -698,13 +719,18 @@ __device__ __forceinline__ void wd_bar() {
   if (NW == 1) __syncwarp(); else __syncthreads();
 }
 
-template <int N, int K, int NW, int MINB, bool LA, bool PBS>
-__global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
+template <int N, int K>
+__host__ __device__ constexpr size_t wd_region_doubles() { return (WdLayout<N, K>::TOTAL + 1) & ~size_t(1); }  // per warp, 16-byte multiple
+
+template <int N, int K, int NW, int MINB, bool LA, bool PBS, int LOCK = 1>
+__global__ void __launch_bounds__(32 * NW * LOCK, MINB) qp_wd_kernel(const QPArgs a) {
   static_assert(!LA || NW == 1, "the look-ahead schedule is a one-warp schedule");
+  static_assert(LOCK == 1 || (NW == 1 && !LA), "lock-step CTAs: one warp per problem, plain columns");
   using L = WdLayout<N, K>;
   constexpr int P = L::P, M = L::M, NT = L::NT, NTN = L::NTN, VPL = L::VPL, STRIDE = N + 2 * M + K;
   static_assert(NW == 1 || NW == 2, "one or two warps per problem");
-  extern __shared__ __align__(16) double sm[];
+  extern __shared__ __align__(16) double sm_base[];
+  double* const sm = sm_base + (LOCK > 1 ? (threadIdx.x >> 5) * wd_region_doubles<N, K>() : 0);
   const int lane = threadIdx.x & 31, warp = NW == 1 ? 0 : (int)(threadIdx.x >> 5), r = lane >> 2, q = lane & 3;
   const bool main_warp = warp == 0, helper = warp == NW - 1;  // NW = 1: the one warp plays both roles
   double* __restrict__ T = sm;
@@ -719,7 +745,8 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
   wd_bar<NW>();
 #endif
 
-  for (long long prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
+  for (long long prob = LOCK > 1 ? (long long)blockIdx.x * LOCK + (threadIdx.x >> 5) : (long long)blockIdx.x; prob < a.batch;
+       prob += (long long)gridDim.x * LOCK) {
     const double* __restrict__ Gp = a.G + prob * (N * N);
     const double* __restrict__ Ap = a.A + prob * (N * K);
     double* __restrict__ vp = a.vars + prob * STRIDE;
@@ -952,7 +979,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
         __syncwarp();
       }
       if (status >= 0) break;
-      bool ok = wd_factor_solve<N, K, NW, LA, PBS>(sm, lane, warp, Gp, Ap);
+      bool ok = wd_factor_solve<N, K, NW, LA, PBS, LOCK>(sm, lane, warp, Gp, Ap);
       if (NW == 2) {
         if (threadIdx.x == 0) *ctl = ok ? 1 : 0;
         __syncthreads();  // also: the back substitution is done, the tiles are free for the next trip's staging
@@ -1032,6 +1059,14 @@ __global__ void __launch_bounds__(32 * NW, MINB) qp_wd_kernel(const QPArgs a) {
       }
     }
     WD_T(8);
+  }
+  if constexpr (LOCK > 1) {
+    // out of problems: keep the barrier count of the warps that still factor (one __syncthreads_or + wd_lock_barriers per
+    // factorization) until every warp of the CTA votes "done"
+    while (__syncthreads_or(0)) {
+#pragma unroll 1
+      for (int i = 0; i < wd_lock_barriers<N, K>(); ++i) __syncthreads();
+    }
   }
 #ifdef MO_WD_TRACE
   if (blockIdx.x == 0 && threadIdx.x == 0)

@@ -1,5 +1,6 @@
 // Launcher of the warp-per-problem DMMA kernel (qp_wdm.cuh) in its own translation unit: the kernel is the one under
 // active tuning and this keeps its rebuild at seconds. Called from dispatch_solve in capi.cu.
+#include <atomic>
 #include <cstdlib>
 
 #include "qp_wdm.cuh"
@@ -26,9 +27,36 @@ namespace mo {
 #define MO_WD_ALT_SHAPES(X)
 #endif
 
+#ifndef MO_WD_LOCK
+#define MO_WD_LOCK 0
+#endif
+static std::atomic<int> g_wd_lock{MO_WD_LOCK};  // mo_debug_set_wd_lock: 1 = lock-step CTAs of MINB warps (measured SLOWER, kept for the A/B), 0 = one-warp CTAs
+
+// Lock-step variant: ONE CTA of MINB warps per SM (the residency of the one-warp kernel), a problem per warp.
+template <int N, int K, int MINB, bool PBS>
+static cudaError_t launch_wd_lock(const QPArgs& a, int sms, cudaStream_t stream) {
+  auto kernel = qp_wd_kernel<N, K, 1, 1, false, PBS, MINB>;
+  constexpr size_t smem = sizeof(double) * wd_region_doubles<N, K>() * MINB;
+  static thread_local int configured_dev = -1;
+  int cur = 0;
+  cudaError_t e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return e;
+  if (configured_dev != cur) {
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured_dev = cur;
+  }
+  const long long want = (a.batch + MINB - 1) / MINB;
+  kernel<<<(int)(want < sms ? want : sms), 32 * MINB, smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
 template <int N, int K, int NW, int MINB, bool LA, bool PBS>
 static cudaError_t launch_wd(const QPArgs& a, int sms, cudaStream_t stream) {
   using L = WdLayout<N, K>;
+  if constexpr (NW == 1 && !LA) {
+    if (g_wd_lock.load()) return launch_wd_lock<N, K, MINB, PBS>(a, sms, stream);
+  }
   auto kernel = qp_wd_kernel<N, K, NW, MINB, LA, PBS>;
   static thread_local int configured_dev = -1;
   static thread_local int bps = 0;
@@ -70,3 +98,7 @@ cudaError_t wd_launch(const QPArgs& a, int sms, cudaStream_t stream) {
 }
 
 }  // namespace mo
+
+// Measurement hook: lock-step CTAs of the warp-per-problem DMMA kernel (1) or one-warp CTAs (0, default). Results are
+// bit-identical; lock-step measured slower (profiles/r02_wd_lockstep_ab.txt). Returns the previous value.
+extern "C" int mo_debug_set_wd_lock(int enabled) { return mo::g_wd_lock.exchange(enabled ? 1 : 0); }

@@ -21,7 +21,7 @@ LIB_PATH = Path(os.environ.get("MINI_OPT_B200_LIB", PKG / "libminiopt_b200.so"))
 EXPORTS = [
     "mo_qp_params_default", "mo_qp_vars_stride", "mo_qp_ip_solve_batch", "mo_qp_ip_solve_batch_host", "mo_qp_ip_solve_batch_host_multi",
     "mo_qp_ip_newton_step_batch", "mo_qp_nullspace_solve_batch", "mo_qp_nullspace_solve_batch_noalloc", "mo_qp_nullspace_solve_batch_host", "mo_qp_kernel_variant", "mo_kernel_launch_count", "mo_last_error_string",
-    "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak", "mo_measure_dmma_peak", "mo_nls_family_dims", "mo_nls_solve_family_batch", "mo_debug_set_tma", "mo_debug_set_tpp_async", "mo_debug_set_dm_kernel", "mo_debug_set_ik_warps", "mo_debug_set_ik_sync",
+    "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak", "mo_measure_dmma_peak", "mo_nls_family_dims", "mo_nls_solve_family_batch", "mo_debug_set_tma", "mo_debug_set_tpp_async", "mo_debug_set_dm_kernel", "mo_debug_set_wd_lock", "mo_debug_set_ik_warps", "mo_debug_set_ik_sync",
     "mo_nls_params_default", "mo_nls_linearize_batch", "mo_chain_fk_batch", "mo_nls_solve_chain_ik_batch",
 ]
 
