@@ -409,7 +409,7 @@ int mo_debug_set_dm_kernel(int which);
 /* Measurement hook: the warp-per-problem DMMA kernel in lock-step CTAs (1; measured slower, profiles/r02_wd_lockstep_ab.txt)
  * or one-warp CTAs (0, default). Bit-identical. */
 int mo_debug_set_wd_lock(int enabled);
-/* Measurement hooks of the lock-step chain-IK kernel: warps per CTA (1, 4, 8, 16; -1 on anything else) and which of the
+/* Measurement hooks of the lock-step chain-IK kernel: warps per CTA (1, 16, 24; -1 on anything else) and which of the
  * two optional CTA barriers of a pass are taken (bit 0: after the linearization, bit 1: after the inner QP). Results are
  * bit-identical for every value. Each returns the previous value. */
 int mo_debug_set_ik_warps(int warps);

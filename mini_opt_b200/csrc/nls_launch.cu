@@ -8,11 +8,11 @@ namespace mo {
 namespace {
 
 #ifndef MO_IK_WARPS
-#define MO_IK_WARPS 16
+#define MO_IK_WARPS 24
 #endif
 std::atomic<int> g_ik_warps{MO_IK_WARPS};  // mo_debug_set_ik_warps
 #ifndef MO_IK_SYNC
-#define MO_IK_SYNC 3
+#define MO_IK_SYNC 1
 #endif
 std::atomic<int> g_ik_sync{MO_IK_SYNC};    // mo_debug_set_ik_sync: CTA barriers after phase A (1) and phase B (2)
 
@@ -73,23 +73,27 @@ int nls_launch_chain_ik(const mo_chain_ik_batch* problems, const mo_nls_params* 
                         const NlsLaunchInfo& dev, cudaStream_t stream, std::string* err) {
   const ChainArgs ca = make_chain_args(problems);
   const int mask = g_ik_sync.load();
-  // warps per CTA marching in lock-step (nls_chain.cuh); W x MINB = 16 resident warps per SM as measured best in round 1
+  // warps per CTA marching in lock-step (nls_chain.cuh), one CTA per SM. Measured (profiles/r02_ik_lockstep_ab.jsonl, 6 links,
+  // 100K problems): 16 warps (128 registers) 90.3 ms, 24 (80 registers, spills) 79.2, 32 (64 registers) 79.9, two CTAs of 16: 87.4
   int w = g_ik_warps.load();
+  if (w == 24) {    // one lock-step CTA of 24 warps per SM (85 registers per thread)
+    if (sizeof(double) * (size_t)nls_per_warp_doubles<ChainFamily>(ca) * 24 <= dev.max_smem_optin)
+      return nls_solve_launch<ChainFamily, 24, 1>(ca, params, out, dev, stream, mask, err);
+    w = 16;
+  }
   while (w > 1 && sizeof(double) * (size_t)nls_per_warp_doubles<ChainFamily>(ca) * w > dev.max_smem_optin) w /= 2;
   switch (w) {
     case 16: return nls_solve_launch<ChainFamily, 16, 1>(ca, params, out, dev, stream, mask, err);
-    case 8: return nls_solve_launch<ChainFamily, 8, 2>(ca, params, out, dev, stream, mask, err);
-    case 4: return nls_solve_launch<ChainFamily, 4, 4>(ca, params, out, dev, stream, mask, err);
     default: return nls_solve_launch<ChainFamily, 1, 16>(ca, params, out, dev, stream, mask, err);
   }
 }
 
 }  // namespace mo
 
-// Measurement hook: warps per CTA of the lock-step chain-IK kernel (1, 2, 4, 8 or 16; 1 = every warp on its own, the
-// round-1 schedule). Returns the previous value. Results do not depend on it (bit-identical), only the time does.
+// Measurement hook: warps per CTA of the lock-step chain-IK kernel (1, 16 or 24; 1 = every warp on its own, the round-1
+// schedule; 24 = the default, 80 registers per thread; shapes whose 24 regions exceed shared memory run with 16). Returns the previous value. Results do not depend on it (bit-identical), only the time does.
 extern "C" int mo_debug_set_ik_warps(int warps) {
-  if (warps != 1 && warps != 4 && warps != 8 && warps != 16) return -1;
+  if (warps != 1 && warps != 16 && warps != 24) return -1;
   return mo::g_ik_warps.exchange(warps);
 }
 

@@ -1,4 +1,4 @@
-"""A/B of the lock-step chain-IK kernel: warps per CTA 1 (round-1 schedule: every warp on its own), 2, 4, 8, 16 through
+"""A/B of the lock-step chain-IK kernel: warps per CTA 1 (round-1 schedule: every warp on its own), 16, 24 through
 mo_debug_set_ik_warps. Results must be bit-identical; only the time may change.
 Usage (GPU box): python tools/ik_ab.py [--links 6 --batch 100000]"""
 import argparse, json, sys
@@ -19,7 +19,7 @@ ch = nls.chain_to_device(synth.chain_ik_batch_numpy(a.links, a.batch, seed=4321,
 prm = synth.chain_ik_params()
 res = {"links": a.links, "batch": a.batch, "n_eq": a.n_eq, "runs": []}
 ref = None
-for w, mask in ((1, 3), (8, 3), (16, 3), (16, 2), (16, 1), (16, 0), (8, 0), (8, 2)):
+for w, mask in ((1, 3), (16, 3), (24, 3), (24, 1), (16, 1)):
     assert L.mo_debug_set_ik_warps(w) >= 1
     L.mo_debug_set_ik_sync(mask)
     out = nls.alloc_nls_out_torch(a.batch, ch.n, dev)
@@ -38,6 +38,6 @@ for w, mask in ((1, 3), (8, 3), (16, 3), (16, 2), (16, 1), (16, 0), (8, 0), (8, 
     same = all((getattr(cur, f) == getattr(ref, f)).all() for f in ("x", "termination", "iterations", "qp_iterations", "ls_steps"))
     res["runs"].append({"warps_per_cta": w, "sync_mask": mask, "ms": ms, "problems_per_s": a.batch / (ms * 1e-3),
                         "qp_steps_per_s": float(cur.qp_iterations.sum()) / (ms * 1e-3), "bit_identical_to_first": bool(same)})
-L.mo_debug_set_ik_warps(16)
-L.mo_debug_set_ik_sync(3)
+L.mo_debug_set_ik_warps(24)
+L.mo_debug_set_ik_sync(1)
 print(json.dumps(res))
