@@ -211,6 +211,39 @@ def test_user_provided_guess_and_flags(dev, oracle):
     compare(out, ref, 8)  # interior user start: measured 1.0
 
 
+@pytest.mark.parametrize("n,k,explicit,variant", [(8, 2, False, "tpp"), (6, 2, False, "warp16"), (8, 2, True, "warp16"),
+                                                 (16, 8, False, "dmma_warp"), (20, 4, False, "generic")])
+def test_nonpositive_slack_status(dev, oracle, n, k, explicit, variant):
+    """F_ASSERT(all s > 0) of ComputeLDLT (qp.cc:285) is a per-problem status here: a USER_PROVIDED start with one slack <= 0
+    ends as MO_QP_NONPOSITIVE_SLACK (3) on every kernel family, its neighbours in the batch are untouched, and the oracle's
+    batched stand-in reports the same."""
+    from mini_opt_b200 import lib
+    B = 96
+    arrs = synth.box_qp_batch_numpy(n, k, B, seed=21, explicit_constraints=explicit)
+    if explicit:
+        arrs.flags = 0  # plain (variable, a, b) triplets: not the box-pair fast path
+    m = 2 * n
+    assert lib.kernel_variant(n, k, m, arrs.flags).startswith(variant), lib.kernel_variant(n, k, m, arrs.flags)
+    rng = np.random.default_rng(3)
+    uv = np.zeros((B, abi.vars_stride(n, k, m)))
+    uv[:, :n] = rng.uniform(-0.5, 0.5, (B, n))
+    uv[:, n:n + m] = rng.uniform(0.1, 1.0, (B, m))
+    uv[:, n + m:n + m + k] = rng.uniform(-1, 1, (B, k))
+    uv[:, n + m + k:] = rng.uniform(0.1, 1.0, (B, m))
+    bad = np.arange(0, B, 7)
+    uv[bad, n + (bad % m)] = -0.25       # a negative slack ...
+    uv[bad[::2], n + (bad[::2] % m)] = 0.0  # ... or exactly zero
+    prm = synth.solve_params(abi.MO_GUESS_USER_PROVIDED)
+    ref, _ = oracle.qp_solve("oracle", arrs, prm, user_vars=uv)
+    out = gpu_solve(arrs, prm, dev, user_vars=uv)
+    good = np.setdiff1d(np.arange(B), bad)
+    assert (out.status[bad] == abi.MO_QP_NONPOSITIVE_SLACK).all(), out.status[bad]
+    assert (ref.status[bad] == abi.MO_QP_NONPOSITIVE_SLACK).all(), ref.status[bad]
+    assert (out.iters[bad] == 0).all()
+    assert np.isin(out.status[good], (abi.MO_QP_SATISFIED_KKT_TOL, abi.MO_QP_MAX_ITERATIONS)).all()
+    assert (out.status[good] == ref.status[good]).mean() >= 0.97
+
+
 def test_max_iterations_and_failures(dev, oracle):
     """MAX_ITERATIONS status, and per-problem failure codes instead of exceptions."""
     arrs = synth.box_qp_batch_numpy(8, 2, 500, seed=11, explicit_constraints=False)
