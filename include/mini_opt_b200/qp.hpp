@@ -357,6 +357,108 @@ class QPInteriorPointSolver {
   Vector variables_;
 };
 
+// ---------------------------------------------------------------------------------------------------------
+// General (non-diagonal) linear inequalities  a . x + b >= 0  (SURVEY 8(f) row 4). The reference does not have them
+// (README.md:36-37 lists them as future work), so there is no reference code path to mirror; they are provided by an EXACT
+// reformulation onto the diagonal form every kernel already solves: one new variable t_j per general constraint,
+//     t_j - a_j . x - b_j = 0   (an equality row),      t_j >= 0   (a diagonal inequality),
+// i.e. the lifted problem has n + g variables, k + g equality rows and m + g diagonal constraints, G' = blkdiag(G, 0).
+// Its KKT conditions are the original problem's with z_j (the multiplier of t_j >= 0) as the multiplier of constraint j:
+// G x + c - A_eq' y - sum_j a_j z_j = 0. Sigma = z / s on the t block makes the reduced Hessian positive definite from the
+// first Newton step on; the equality-constrained initial guess would factor blkdiag(G, 0) without Sigma (a zero pivot in
+// the unpivoted kernels), so the start point is built on the host instead: x0 = the reference's naive start (0 clamped into
+// the diagonal constraints, qp.cc:462-481), t0 = max(a . x0 + b, 1), s = t0, z = 1 / t0.
+// ---------------------------------------------------------------------------------------------------------
+struct GeneralInequality {
+  Vector a;  // n coefficients
+  double b;
+  double Evaluate(const Vector& x) const {
+    double v = b;
+    for (std::size_t i = 0; i < a.size(); ++i) v += a[i] * x[i];
+    return v;
+  }
+};
+
+inline QP LiftGeneralInequalities(const QP& qp, const std::vector<GeneralInequality>& general) {
+  const int n = qp.G.rows(), k = qp.A_eq.rows(), g = static_cast<int>(general.size());
+  QP out(n + g);
+  for (int c = 0; c < n; ++c)
+    for (int r = 0; r < n; ++r) out.G(r, c) = qp.G(r, c);
+  for (int i = 0; i < n; ++i) out.c[i] = qp.c[i];
+  out.A_eq.resize(k + g, n + g);
+  out.b_eq = Vector(static_cast<std::size_t>(k + g), 0.0);
+  for (int r = 0; r < k; ++r) {
+    for (int c = 0; c < n; ++c) out.A_eq(r, c) = qp.A_eq(r, c);
+    out.b_eq[r] = qp.b_eq[r];
+  }
+  out.constraints = qp.constraints;
+  for (int j = 0; j < g; ++j) {
+    if (static_cast<int>(general[j].a.size()) != n) throw std::invalid_argument("GeneralInequality: a must have n entries");
+    for (int c = 0; c < n; ++c) out.A_eq(k + j, c) = -general[j].a[c];
+    out.A_eq(k + j, n + j) = 1.0;
+    out.b_eq[k + j] = -general[j].b;
+    out.constraints.push_back(Var(n + j) >= 0.0);
+  }
+  return out;
+}
+
+// Solves a batch of QPs with general inequalities (every problem: the same n, k, m and the same NUMBER of general
+// constraints). The outputs are in the ORIGINAL problem's terms with the general constraints appended to the diagonal ones:
+// variables = [x (n) | s (m + g) | y (k) | z (m + g)], n / k / m set accordingly.
+inline std::vector<QPInteriorPointSolverOutputs> SolveBatchWithGeneralInequalities(
+    const std::vector<QP>& qps, const std::vector<std::vector<GeneralInequality>>& general,
+    QPInteriorPointSolver::Params params, int device = 0) {
+  if (qps.size() != general.size()) throw std::invalid_argument("one list of general inequalities per problem");
+  std::vector<QP> lifted;
+  std::vector<Vector> start;
+  lifted.reserve(qps.size());
+  for (std::size_t p = 0; p < qps.size(); ++p) {
+    const QP& q = qps[p];
+    const int n = q.G.rows(), k = q.A_eq.rows(), m = static_cast<int>(q.constraints.size()), g = static_cast<int>(general[p].size());
+    lifted.push_back(LiftGeneralInequalities(q, general[p]));
+    Vector x0(static_cast<std::size_t>(n), 0.0);
+    for (const LinearInequalityConstraint& con : q.constraints) x0[con.variable] = con.ClampX(x0[con.variable]);
+    Vector v(static_cast<std::size_t>(n + g + 2 * (m + g) + k + g), 0.0);  // [x, t | s | y | z] of the lifted problem
+    for (int i = 0; i < n; ++i) v[i] = x0[i];
+    double* sv = v.data() + n + g;
+    double* zv = v.data() + n + g + (m + g) + (k + g);
+    for (int i = 0; i < m; ++i) {
+      const LinearInequalityConstraint& con = q.constraints[i];
+      const double s = con.a * x0[con.variable] + con.b;
+      sv[i] = s > 1.0e-9 ? s : 1.0e-9;
+      zv[i] = 1.0 / sv[i];
+    }
+    for (int j = 0; j < g; ++j) {
+      const double t = general[p][j].Evaluate(x0);
+      v[n + j] = t > 1.0 ? t : 1.0;
+      sv[m + j] = v[n + j];
+      zv[m + j] = 1.0 / sv[m + j];
+    }
+    start.push_back(std::move(v));
+  }
+  params.initial_guess_method = InitialGuessMethod::USER_PROVIDED;
+  std::vector<QPInteriorPointSolverOutputs> sol = QPInteriorPointSolver::SolveBatch(lifted, params, device, &start);
+  for (std::size_t p = 0; p < qps.size(); ++p) {
+    const QP& q = qps[p];
+    const int n = q.G.rows(), k = q.A_eq.rows(), m = static_cast<int>(q.constraints.size()), g = static_cast<int>(general[p].size());
+    const Vector& lv = sol[p].variables;
+    Vector v;
+    v.insert(v.end(), lv.begin(), lv.begin() + n);                                    // x
+    v.insert(v.end(), lv.begin() + n + g, lv.begin() + n + g + m + g);                // s (diagonal, then general)
+    v.insert(v.end(), lv.begin() + n + g + m + g, lv.begin() + n + g + m + g + k);    // y of the original equality rows
+    v.insert(v.end(), lv.begin() + n + g + m + g + k + g, lv.end());                  // z
+    sol[p].variables = std::move(v);
+    sol[p].n = n; sol[p].k = k; sol[p].m = m + g;
+    if (k == 0) sol[p].lagrange_multipliers.reset();
+    else {  // the summary over the ORIGINAL equality rows only (qp.cc:539-546)
+      double mn = sol[p].y(0), li = std::fabs(sol[p].y(0));
+      for (int r = 1; r < k; ++r) { mn = sol[p].y(r) < mn ? sol[p].y(r) : mn; li = std::fabs(sol[p].y(r)) > li ? std::fabs(sol[p].y(r)) : li; }
+      sol[p].lagrange_multipliers = QPLagrangeMultipliers{mn, li};
+    }
+  }
+  return sol;
+}
+
 enum class QPNullSpaceTerminationState { SUCCESS = 0, NOT_POSITIVE_DEFINITE = 1 };  // structs.hpp:137-142
 inline const char* ToString(QPNullSpaceTerminationState s) {                         // structs.cc:38-48
   return s == QPNullSpaceTerminationState::SUCCESS ? "SUCCESS" : "NOT_POSITIVE_DEFINITE";

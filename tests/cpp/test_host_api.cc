@@ -98,6 +98,78 @@ int main(int argc, char** argv) {
     flat.G = Matrix(2, 2);  // reduced Hessian 0 -> NOT_POSITIVE_DEFINITE
     CHECK(nss.Solve(flat) == QPNullSpaceTerminationState::NOT_POSITIVE_DEFINITE);
   }
+  // General inequalities through the exact lifting (SolveBatchWithGeneralInequalities; the reference has none, README.md:36-37):
+  // min (x-2)^2 + (y-2)^2  s.t.  x + y <= 2, x >= 0, y >= 0  ->  (1, 1), multiplier of the general constraint 2
+  {
+    QP tri(2);
+    tri.G(0, 0) = 2.0; tri.G(1, 1) = 2.0; tri.c[0] = -4.0; tri.c[1] = -4.0;
+    tri.constraints = {Var(0) >= 0.0, Var(1) >= 0.0};
+    const std::vector<GeneralInequality> gen = {GeneralInequality{Vector{-1.0, -1.0}, 2.0}};
+    QPInteriorPointSolver::Params gp;
+    gp.max_iterations = 40;
+    gp.sigma = 0.1;
+    const auto r1 = SolveBatchWithGeneralInequalities({tri}, {gen}, gp);
+    CHECK(r1[0].termination_state == QPInteriorPointTerminationState::SATISFIED_KKT_TOL && r1[0].n == 2 && r1[0].m == 3 && r1[0].k == 0);
+    CHECK(std::fabs(r1[0].x(0) - 1.0) < 1e-6 && std::fabs(r1[0].x(1) - 1.0) < 1e-6);
+    CHECK(std::fabs(r1[0].z(2) - 2.0) < 1e-5 && std::fabs(r1[0].s(2)) < 1e-6 && r1[0].z(0) < 1e-6);
+    // a batch of random 6-variable problems, 1 equality row, box on every variable, 4 general constraints: the KKT
+    // conditions of the ORIGINAL problem hold at the returned point
+    std::vector<QP> qps;
+    std::vector<std::vector<GeneralInequality>> gens;
+    unsigned long long st = 12345;
+    auto rnd = [&st]() { st = st * 6364136223846793005ULL + 1442695040888963407ULL; return (double)((st >> 11) & 0xFFFFFFFFFFFFFULL) / 4503599627370496.0 * 2.0 - 1.0; };
+    for (int p = 0; p < 64; ++p) {
+      const int n = 6;
+      QP q(n);
+      double Mx[6][6];
+      for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) Mx[i][j] = rnd();
+      for (int i = 0; i < n; ++i)
+        for (int j = 0; j <= i; ++j) {
+          double acc = i == j ? 1.0 : 0.0;
+          for (int l = 0; l < n; ++l) acc += Mx[i][l] * Mx[j][l];
+          q.G(i, j) = acc; q.G(j, i) = acc;
+        }
+      for (int i = 0; i < n; ++i) q.c[i] = 3.0 * rnd();
+      q.A_eq.resize(1, n);
+      for (int j = 0; j < n; ++j) q.A_eq(0, j) = rnd();
+      q.b_eq = Vector{0.1 * rnd()};
+      for (int i = 0; i < n; ++i) { q.constraints.push_back(Var(i) >= -1.0); q.constraints.push_back(Var(i) <= 1.0); }
+      std::vector<GeneralInequality> g;
+      for (int j = 0; j < 4; ++j) {
+        GeneralInequality gi{Vector(n, 0.0), 0.5 + 0.25 * rnd()};
+        for (int i = 0; i < n; ++i) gi.a[i] = rnd();
+        g.push_back(gi);
+      }
+      qps.push_back(q);
+      gens.push_back(g);
+    }
+    const auto rb = SolveBatchWithGeneralInequalities(qps, gens, gp);
+    int converged = 0;
+    for (std::size_t p = 0; p < qps.size(); ++p) {
+      const QPInteriorPointSolverOutputs& o = rb[p];
+      if (o.termination_state != QPInteriorPointTerminationState::SATISFIED_KKT_TOL) continue;
+      ++converged;
+      CHECK(o.n == 6 && o.k == 1 && o.m == 16);
+      Vector x(6);
+      for (int i = 0; i < 6; ++i) x[i] = o.x(i);
+      for (int i = 0; i < 6; ++i) {  // stationarity: G x + c - A' y - sum a_i z_i (diagonal: a = +-1 on variable i/2; general: dense)
+        double rsd = qps[p].c[i] - qps[p].A_eq(0, i) * o.y(0);
+        for (int j = 0; j < 6; ++j) rsd += qps[p].G(i, j) * x[j];
+        rsd -= o.z(2 * i) - o.z(2 * i + 1);
+        for (int j = 0; j < 4; ++j) rsd -= gens[p][j].a[i] * o.z(12 + j);
+        CHECK(std::fabs(rsd) < 1e-6);
+      }
+      double eq = qps[p].b_eq[0];
+      for (int j = 0; j < 6; ++j) eq += qps[p].A_eq(0, j) * x[j];
+      CHECK(std::fabs(eq) < 1e-7);
+      for (int j = 0; j < 4; ++j) {
+        const double v = gens[p][j].Evaluate(x);
+        CHECK(v > -1e-7 && o.z(12 + j) >= 0.0 && std::fabs(v * o.z(12 + j)) < 1e-5 && std::fabs(v - o.s(12 + j)) < 1e-7);
+      }
+      for (int i = 0; i < 6; ++i) CHECK(x[i] > -1.0 - 1e-7 && x[i] < 1.0 + 1e-7);
+    }
+    CHECK(converged >= 62);
+  }
   std::printf("gpu ok\n");
   return 0;
 }
