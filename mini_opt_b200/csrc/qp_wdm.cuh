@@ -97,7 +97,7 @@ __device__ __forceinline__ double wd_sum_r(double v) {
 // in a DMMA phase (panel solve of column J + gather of column J+1, all warps) or in a pivot-chain phase (diagonal block J,
 // all warps). Why: DMMA.8x8x4 holds the FP64 pipe of a sub-partition for 16 cycles; with the phases of the resident warps
 // interleaved at random every dependent DFMA of a pivot chain queues behind other warps' DMMAs (16-25 cycles per dependent
-// operation instead of 8, profiles/r02_lanes_microbench.txt), and the chain is 37 % of the kernel
+// operation instead of 8, profiles/r02_wd_variants.txt, last lines: tools/ubench/lanes_bench.cu), and the chain is 37 % of the kernel
 // (profiles/r02_wd64_phase_trace.txt). The barriers order nothing -- no data is shared between the warps.
 // MEASURED (profiles/r02_wd_lockstep_ab.txt): the hypothesis is wrong for this kernel. With every warp of the SM in its
 // pivot-chain phase at once the diagonal blocks take exactly as long (1.60M cycles of a 4.4M-cycle launch either way): the
