@@ -466,6 +466,15 @@ static __device__ unsigned long long g_ik_tickets[kIkTicketSlots];  // one ring 
 // the QP, line search evaluations) have bodies that fit the cache once nobody else is evicting them. The arithmetic of a
 // problem is untouched: results are bit-identical to the W = 1 schedule. Cost: warps idle at the barriers while the slowest
 // QP / line search of the CTA finishes.
+#ifdef MO_IK_TRACE
+// Debug build only: lane 0 of warp 0 of CTA 0 accumulates cycles per phase of the lock-step pass and prints them at kernel end.
+__shared__ long long s_ik_tr[8];
+__shared__ long long s_ik_t0;
+#define IK_T(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long t_ = clock64(); s_ik_tr[i] += t_ - s_ik_t0; s_ik_t0 = t_; } } while (0)
+#else
+#define IK_T(i) do {} while (0)
+#endif
+
 template <class F, int W, int MINB>
 __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename F::Args a, const NlsParams prm, const NlsOut out,
                                                                  unsigned long long* __restrict__ ticket,
@@ -519,7 +528,11 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
     __syncwarp();
     busy = false;
   };
+#ifdef MO_IK_TRACE
+  if (threadIdx.x == 0) { for (int i = 0; i < 8; ++i) s_ik_tr[i] = 0; s_ik_t0 = clock64(); }
+#endif
   for (;;) {
+    IK_T(6);  // finish() of the previous pass
     // ---- fetch: an idle warp takes the next problem of the batch ----
     while (!busy && !drained) {
       unsigned long long t = 0;
@@ -534,8 +547,10 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
       busy = true;
       if (prm.max_iterations <= 0) finish();  // the Solve loop never runs: MAX_ITERATIONS at x0
     }
+    IK_T(0);  // fetch
     if (W > 1) { if (!__syncthreads_or(busy ? 1 : 0)) break; }
     else if (!busy) break;
+    IK_T(1);  // wait at the barrier that opens the pass
     bool ended = false;  // this problem terminates in this pass
     double pre_f = 0.0, pre_eq = 0.0;
     // ---- phase A: LinearizeAndFillQP (nonlinear.cc:170-214) ----
@@ -546,7 +561,9 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
                      A, bvec, W_.cb, err);
       pre_f = err[0]; pre_eq = err[1];
     }
+    IK_T(2);  // phase A
     if (W > 1 && (sync_mask & 1)) __syncthreads();  // uniform over the CTA: a kernel argument
+    IK_T(3);  // wait after A
     // ---- phase B: ComputeStepDirection (nonlinear.cc:216-259): Setup + Solve on the QP in shared memory ----
     if (busy) {
       for (int i = lane; i < W_.T; i += 32) W_.vars[i] = 0.0;
@@ -569,6 +586,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
       }
       __syncwarp();
     }
+    IK_T(4);  // phase B
     if (W > 1 && (sync_mask & 2)) __syncthreads();
     // ---- phase C: derivatives, penalty, line search, lambda update ----
     if (busy && !ended) {
@@ -666,8 +684,14 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
       if (exit_state >= 0) { term = exit_state; ended = true; }
       else if (iter >= prm.max_iterations) ended = true;  // term stays MAX_ITERATIONS
     }
+    IK_T(5);  // phase C (with the wait after B when that barrier is on)
     if (busy && ended) finish();
   }
+#ifdef MO_IK_TRACE
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    printf("ik trace W=%d: fetch %lld | wait(open) %lld | A linearize %lld | wait(A) %lld | B qp %lld | C line search %lld | finish %lld\n", W,
+           s_ik_tr[0], s_ik_tr[1], s_ik_tr[2], s_ik_tr[3], s_ik_tr[4], s_ik_tr[5], s_ik_tr[6]);
+#endif
 }
 
 template <int W, int MINB>
