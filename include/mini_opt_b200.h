@@ -410,7 +410,8 @@ int mo_debug_set_dm_kernel(int which);
  * or one-warp CTAs (0, default). Bit-identical. */
 int mo_debug_set_wd_lock(int enabled);
 /* Measurement hooks of the lock-step chain-IK kernel: warps per CTA (1, 16, 24; -1 on anything else) and which of the
- * two optional CTA barriers of a pass are taken (bit 0: after the linearization, bit 1: after the inner QP). Results are
+ * two optional CTA barriers of a pass are taken (bit 0: after the linearization, bit 1: after the inner QP; bits 2-3: the
+ * opening barrier only every 2nd / 4th pass). Results are
  * bit-identical for every value. Each returns the previous value. */
 int mo_debug_set_ik_warps(int warps);
 int mo_debug_set_ik_sync(int mask);

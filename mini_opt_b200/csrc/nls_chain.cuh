@@ -510,6 +510,7 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
   // state of this warp's problem (uniform over the lanes)
   long long p = -1;
   bool busy = false, drained = false;
+  int pass_no = 0;
   int state = 0, term = MO_NLS_MAX_ITERATIONS, iters = 0, qp_total = 0, ls_total = 0, iter = 0;
   double lambda = 0.0, penalty = 0.0;
   // results of problem p: x, the errors at x, the counters
@@ -548,8 +549,12 @@ __global__ void __launch_bounds__(32 * W, MINB) nls_solve_kernel(const typename 
       if (prm.max_iterations <= 0) finish();  // the Solve loop never runs: MAX_ITERATIONS at x0
     }
     IK_T(0);  // fetch
-    if (W > 1) { if (!__syncthreads_or(busy ? 1 : 0)) break; }
-    else if (!busy) break;
+    // sync_mask bits 2-3: the opening barrier (which is also the CTA's "anyone still busy" vote) only every 2nd / 4th pass;
+    // in between the warps run on, a drained warp idles until the next vote
+    if (W > 1) {
+      const int skip = (sync_mask >> 2) & 3;
+      if ((pass_no++ & skip) == 0) { if (!__syncthreads_or(busy ? 1 : 0)) break; }
+    } else if (!busy) break;
     IK_T(1);  // wait at the barrier that opens the pass
     bool ended = false;  // this problem terminates in this pass
     double pre_f = 0.0, pre_eq = 0.0;

@@ -99,4 +99,4 @@ extern "C" int mo_debug_set_ik_warps(int warps) {
 
 // Measurement hook: which of the two optional CTA barriers of a lock-step pass are taken (bit 0: after the linearization,
 // bit 1: after the inner QP); the barrier at the top of a pass always is. Results do not depend on it.
-extern "C" int mo_debug_set_ik_sync(int mask) { return mo::g_ik_sync.exchange(mask & 3); }
+extern "C" int mo_debug_set_ik_sync(int mask) { return mo::g_ik_sync.exchange(mask & 15); }

@@ -19,7 +19,7 @@ ch = nls.chain_to_device(synth.chain_ik_batch_numpy(a.links, a.batch, seed=4321,
 prm = synth.chain_ik_params()
 res = {"links": a.links, "batch": a.batch, "n_eq": a.n_eq, "runs": []}
 ref = None
-for w, mask in ((1, 3), (16, 3), (24, 3), (24, 1), (16, 1)):
+for w, mask in ((1, 3), (24, 1), (24, 5), (24, 13), (24, 4), (24, 1)):
     assert L.mo_debug_set_ik_warps(w) >= 1
     L.mo_debug_set_ik_sync(mask)
     out = nls.alloc_nls_out_torch(a.batch, ch.n, dev)
