@@ -271,6 +271,32 @@ Residual MakeResidual(const std::array<int, P>& index, F&& f) {
   return Residual(std::make_shared<Residual::Model<R, P, std::decay_t<F>>>(index, std::forward<F>(f)));
 }
 
+#ifdef MINI_OPT_B200_WITH_EIGEN
+}  // namespace mini_opt_b200
+#include <Eigen/Core>
+namespace mini_opt_b200 {
+// With Eigen on the include path (-DMINI_OPT_B200_WITH_EIGEN): residual functors with the REFERENCE's signature
+// (residual.hpp:121-143)   Eigen::Matrix<double, R, 1> f(const Eigen::Matrix<double, P, 1>&, Eigen::Matrix<double, R, P>* J)
+// are accepted as they are: a reference user's MakeResidual<R, P>(index, functor) call keeps compiling.
+template <int R, int P, class F>
+Residual MakeResidualEigen(const std::array<int, P>& index, F f) {
+  return MakeResidual<R, P>(index, [f](const std::array<double, P>& params, std::array<double, R * P>* J) {
+    Eigen::Matrix<double, P, 1> x;
+    for (int i = 0; i < P; ++i) x[i] = params[i];
+    Eigen::Matrix<double, R, P> Jm;
+    const Eigen::Matrix<double, R, 1> r = f(x, J ? &Jm : nullptr);
+    if (J)
+      for (int c = 0; c < P; ++c)
+        for (int i = 0; i < R; ++i) (*J)[c * R + i] = Jm(i, c);  // column-major, like Eigen's default
+    std::array<double, R> out;
+    for (int i = 0; i < R; ++i) out[i] = r[i];
+    return out;
+  });
+}
+inline Eigen::VectorXd ToEigen(const Vector& v) { return Eigen::Map<const Eigen::VectorXd>(v.data(), static_cast<Eigen::Index>(v.size())); }
+inline Vector FromEigen(const Eigen::VectorXd& v) { return Vector(v.data(), v.data() + v.size()); }
+#endif
+
 // nonlinear.hpp:24-35: min sum 1/2 |f_i(x)|^2  s.t.  c_j(x) = 0,  a x[v] + b >= 0
 struct Problem {
   int dimension{0};
@@ -307,6 +333,10 @@ class ConstrainedNonlinearLeastSquares {
   };
   // nonlinear.hpp:127: x <- x (+) alpha * dx
   using Retraction = std::function<void(Vector& x, const Vector& dx, double alpha)>;
+  // nonlinear.hpp:150-153 / nonlinear.cc:145-151: called after every outer iteration; returning false ends the problem with
+  // USER_CALLBACK unless that iteration terminated it anyway. Batched form: (problem index in the batch, the iteration).
+  using ExitCallback = std::function<bool(const NLSIteration&)>;
+  using BatchExitCallback = std::function<bool(std::size_t, const NLSIteration&)>;
 
   explicit ConstrainedNonlinearLeastSquares(const Problem* problem, Retraction retraction = nullptr)
       : p_(problem), custom_retraction_(std::move(retraction)) {
@@ -315,7 +345,9 @@ class ConstrainedNonlinearLeastSquares {
 
   // One problem = a batch of one.
   NLSSolverOutputs Solve(const Params& params, const Vector& variables, int device = 0) {
-    std::vector<NLSSolverOutputs> out = SolveBatch({p_}, params, {variables}, custom_retraction_, device);
+    BatchExitCallback cb;
+    if (user_exit_callback_) cb = [this](std::size_t, const NLSIteration& it) { return user_exit_callback_(it); };
+    std::vector<NLSSolverOutputs> out = SolveBatch({p_}, params, {variables}, custom_retraction_, device, cb);
     variables_ = out[0].variables;
     if (out[0].termination_state == NLSTerminationState::QP_FAILED) {  // one problem: throw like the reference
       if (out[0].qp_failure_status == MO_QP_NONPOSITIVE_SLACK) throw std::runtime_error("Some slack variables s <= 0");
@@ -324,6 +356,8 @@ class ConstrainedNonlinearLeastSquares {
     return std::move(out[0]);
   }
   const Vector& variables() const { return variables_; }
+  template <typename T>
+  void SetUserExitCallback(T&& cb) { user_exit_callback_ = std::forward<T>(cb); }
 
   // nonlinear.cc:279-293
   static Errors EvaluateNonlinearErrors(const Problem& problem, const Vector& vars) {
@@ -373,7 +407,8 @@ class ConstrainedNonlinearLeastSquares {
   // each. The QPs of all active problems are solved in one device call per outer iteration.
   static std::vector<NLSSolverOutputs> SolveBatch(const std::vector<const Problem*>& problems, const Params& params,
                                                   const std::vector<Vector>& initial_variables,
-                                                  const Retraction& retraction = nullptr, int device = 0) {
+                                                  const Retraction& retraction = nullptr, int device = 0,
+                                                  const BatchExitCallback& exit_callback = nullptr) {
     CheckParams(params);
     const std::size_t B = problems.size();
     if (initial_variables.size() != B) throw std::invalid_argument("one start point per problem");
@@ -491,6 +526,10 @@ class ConstrainedNonlinearLeastSquares {
                                                  q.num_iterations, dd, s.penalty, step, std::move(steps), {}});
         if (null_space) out[i].iterations.back().qp_outputs = QPNullSpaceTerminationState::SUCCESS;
         else out[i].iterations.back().qp_outputs = q;
+        if (exit_callback && !exit_callback(i, out[i].iterations.back()) && !maybe_exit) {  // nonlinear.cc:145-151
+          out[i].termination_state = NLSTerminationState::USER_CALLBACK;
+          s.done = true;
+        }
         if (maybe_exit) {
           out[i].termination_state = *maybe_exit;
           s.done = true;
@@ -606,6 +645,7 @@ class ConstrainedNonlinearLeastSquares {
 
   const Problem* p_;
   Retraction custom_retraction_;
+  ExitCallback user_exit_callback_;
   Vector variables_;
 };
 

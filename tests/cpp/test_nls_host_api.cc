@@ -103,6 +103,16 @@ static void TestRosenbrock(bool lm) {  // nonlinear_test.cc:391-460
   const NLSSolverOutputs one = nls.Solve(p, guesses[1]);
   CHECK(one.termination_state == out[1].termination_state && one.iterations.size() == out[1].iterations.size());
   CHECK(nls.variables()[0] == out[1].variables[0] && nls.variables()[1] == out[1].variables[1]);
+  // SetUserExitCallback (nonlinear.hpp:150-153, nonlinear.cc:145-151): returning false after the first iteration ends the
+  // solve with USER_CALLBACK and exactly one logged iteration; returning true changes nothing
+  int calls = 0;
+  nls.SetUserExitCallback([&calls](const NLSIteration& it) { ++calls; return it.iteration < 0; });
+  const NLSSolverOutputs stopped = nls.Solve(p, guesses[1]);
+  CHECK(stopped.termination_state == NLSTerminationState::USER_CALLBACK && stopped.iterations.size() == 1 && calls == 1);
+  nls.SetUserExitCallback([&calls](const NLSIteration&) { ++calls; return true; });
+  const NLSSolverOutputs again = nls.Solve(p, guesses[1]);
+  CHECK(again.termination_state == one.termination_state && again.iterations.size() == one.iterations.size());
+  CHECK(calls == 1 + static_cast<int>(one.iterations.size()));
 }
 
 static void TestInequalityConstrainedRosenbrock() {  // nonlinear_test.cc:463-500
