@@ -393,27 +393,9 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
 #pragma unroll
   for (int i = 0; i < KD; ++i) y[i] = 0.0;
 
-  for (;;) {
-    if constexpr (ASYNC) {
-      // ======== (0) lanes whose copies were issued one round ago join ========
-      if (__any_sync(FULL, loading)) {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        __syncwarp();
-        if (loading) {
-          const double* __restrict__ st = xy_stage + xy_slot * (N + K);
-#pragma unroll
-          for (int i = 0; i < N; ++i) x[i] = st[i];
-#pragma unroll
-          for (int r = 0; r < K; ++r) y[r] = st[N + r];
-          live = st_in != MO_QP_FAILED_FACTORIZATION;
-          first = true;
-          iters = 0;
-          alpha_p = 1.0; alpha_d = 1.0;
-          loading = false;
-        }
-        __syncwarp();  // the staging rows are free again
-      }
-    }
+  // (1) as a closure: the cp.async schedule runs it in the MIDDLE of a round (right after the termination test), the register
+  // schedule at the top of a round
+  auto writeout_and_refill = [&]() {
     // ======== (1) write out finished problems, refill idle lanes ========
     unsigned fmask = __ballot_sync(FULL, fin);
     while (fmask) {  // [x|s|y|z] of lane `src`: x, y parked in slots [0, N+K) of its column, s, z in place
@@ -579,9 +561,61 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
       }
       __syncwarp();
     }
-    if (!__any_sync(FULL, live)) {
-      if (next >= wend && !__any_sync(FULL, loading)) break;
-      continue;
+  };
+  // (5) as a closure: this lane's problem ended -- park x, y for the warp's coalesced store, scalar outputs
+  auto park_finished = [&](const int done_status) {
+      // ======== (5) this lane's problem ended: park x, y for the warp's coalesced store, scalar outputs ========
+#pragma unroll
+      for (int i = 0; i < N; ++i) smcol[i * LD] = x[i];
+#pragma unroll
+      for (int r = 0; r < K; ++r) smcol[(N + r) * LD] = y[r];
+      a.status[prob] = done_status;
+      a.iters[prob] = iters;
+      if (done_status >= MO_QP_FAILED_FACTORIZATION && a.kkt_final) {
+        double* __restrict__ kf = a.kkt_final + prob * 4;
+        kf[0] = 0.0; kf[1] = 0.0; kf[2] = 0.0; kf[3] = 0.0;
+      }
+      if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
+        double mn = qnan(), li = qnan();
+        if (K > 0) {
+          mn = y[0]; li = fabs(y[0]);
+#pragma unroll
+          for (int r = 1; r < K; ++r) { mn = y[r] < mn ? y[r] : mn; li = fabs(y[r]) > li ? fabs(y[r]) : li; }
+        }
+        a.lagrange[prob * 2] = mn;
+        a.lagrange[prob * 2 + 1] = li;
+      }
+      fin = true;
+      live = false;
+  };
+
+  for (;;) {
+    if constexpr (ASYNC) {
+      // ======== (0) lanes whose copies were issued one round ago join ========
+      if (__any_sync(FULL, loading)) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        if (loading) {
+          const double* __restrict__ st = xy_stage + xy_slot * (N + K);
+#pragma unroll
+          for (int i = 0; i < N; ++i) x[i] = st[i];
+#pragma unroll
+          for (int r = 0; r < K; ++r) y[r] = st[N + r];
+          live = st_in != MO_QP_FAILED_FACTORIZATION;
+          first = true;
+          iters = 0;
+          alpha_p = 1.0; alpha_d = 1.0;
+          loading = false;
+        }
+        __syncwarp();  // the staging rows are free again
+      }
+    }
+    if constexpr (!ASYNC) {
+      writeout_and_refill();
+      if (!__any_sync(FULL, live)) {
+        if (next >= wend && !__any_sync(FULL, loading)) break;
+        continue;
+      }
     }
     int done_status = -1;
     double rhs[P], hd[N];  // right-hand side, diagonal of G + Sigma
@@ -676,6 +710,19 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
       for (int v = 0; v < N; ++v) rhs[v] = -fma(-mu, tv[v], base[v]);
     }
 
+    if constexpr (ASYNC) {
+      // The termination test sits at the top of a round, so a lane that just ended is known HERE, with three quarters of
+      // the round (LDL', solve, update) still ahead: its result is written out and the copies of its next problem are
+      // issued now, they land under the rest of this round and the lane joins at the top of the next one -- a finished
+      // lane costs no extra idle round (it cost one when (1) ran at the top of the following round).
+      if (live && done_status >= 0) park_finished(done_status);
+      __syncwarp();  // parked x, y are visible to the lanes that write them out
+      writeout_and_refill();
+      if (!__any_sync(FULL, live)) {
+        if (next >= wend && !__any_sync(FULL, loading)) break;
+        continue;
+      }
+    }
     // ======== (3) reduced KKT matrix [[G + Sigma, .],[A, 0]] (qp.cc:289-297) into registers, LDL', solve:
     //              rhs <- [dx; -dy]. Only the diagonal differs from the copy in shared memory. ========
     double Km[L::NK];
@@ -730,31 +777,7 @@ __global__ void __launch_bounds__(32 * WPB, MINB) qp_tpp_iterate_kernel(const QP
       }
     }
 
-    if (live && done_status >= 0) {
-      // ======== (5) this lane's problem ended: park x, y for the warp's coalesced store, scalar outputs ========
-#pragma unroll
-      for (int i = 0; i < N; ++i) smcol[i * LD] = x[i];
-#pragma unroll
-      for (int r = 0; r < K; ++r) smcol[(N + r) * LD] = y[r];
-      a.status[prob] = done_status;
-      a.iters[prob] = iters;
-      if (done_status >= MO_QP_FAILED_FACTORIZATION && a.kkt_final) {
-        double* __restrict__ kf = a.kkt_final + prob * 4;
-        kf[0] = 0.0; kf[1] = 0.0; kf[2] = 0.0; kf[3] = 0.0;
-      }
-      if (a.lagrange) {  // ComputeLagrangeMultiplierSummary, qp.cc:539-546
-        double mn = qnan(), li = qnan();
-        if (K > 0) {
-          mn = y[0]; li = fabs(y[0]);
-#pragma unroll
-          for (int r = 1; r < K; ++r) { mn = y[r] < mn ? y[r] : mn; li = fabs(y[r]) > li ? fabs(y[r]) : li; }
-        }
-        a.lagrange[prob * 2] = mn;
-        a.lagrange[prob * 2 + 1] = li;
-      }
-      fin = true;
-      live = false;
-    }
+    if (live && done_status >= 0) park_finished(done_status);  // cp.async schedule: only a failed factorization gets here
     __syncwarp();
   }
 }
