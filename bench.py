@@ -170,10 +170,11 @@ def run_reference_qp(arrs_host, prm, threads):
                 cores=threads if kind == "reference" else 1)
 
 
-def pinned_copy(L, arr):
-    """Copy a numpy array into pinned host memory obtained from the library; returns (ndarray view, ptr)."""
+def pinned_copy(L, arr, interleaved=False):
+    """Copy a numpy array into pinned host memory obtained from the library; returns (ndarray view, ptr).
+    interleaved: pages spread over the host's NUMA nodes (buffers that feed several GPUs from one process)."""
     import ctypes as C
-    ptr = L.mo_host_alloc(arr.nbytes)
+    ptr = (L.mo_host_alloc_interleaved if interleaved else L.mo_host_alloc)(arr.nbytes)
     if not ptr:
         raise RuntimeError("mo_host_alloc failed")
     buf = (C.c_char * arr.nbytes).from_address(ptr)

@@ -154,6 +154,9 @@ int mo_qp_ip_solve_batch_host_multi(const mo_qp_batch* problems, const mo_qp_par
 /* Pinned (page-locked) host memory: buffers allocated here are DMA'd directly by the *_host entry points;
  * pageable buffers work too but are staged by the driver. */
 void* mo_host_alloc(size_t bytes);
+/* The same, with the pages interleaved over all NUMA nodes of the host: for buffers that feed several GPUs from one process
+ * (mo_qp_ip_solve_batch_host_multi). Falls back to mo_host_alloc where the policy cannot be set. */
+void* mo_host_alloc_interleaved(size_t bytes);
 void mo_host_free(void* p);
 
 /*

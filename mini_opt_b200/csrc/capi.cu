@@ -2,6 +2,9 @@
 // and the host-buffer convenience entry point. No torch, no Eigen: plain CUDA runtime.
 #include <nvtx3/nvToolsExt.h>
 
+#include <sys/syscall.h>
+#include <unistd.h>
+
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -645,6 +648,32 @@ void* mo_host_alloc(size_t bytes) {
 
 void mo_host_free(void* p) {
   if (p) cudaFreeHost(p);
+}
+
+// Pinned memory whose pages are spread round-robin over all NUMA nodes of the host (set_mempolicy(MPOL_INTERLEAVE) around
+// the allocation, raw syscall: no libnuma in the image). For batches that feed SEVERAL GPUs from one process: a plain
+// allocation lands on the node of the allocating thread and every GPU's DMA then drains that one node's memory controllers
+// (measured: 114 GB/s aggregate over 4 GPUs against 190 GB/s for four processes with their own buffers). Falls back to
+// mo_host_alloc when the policy cannot be set (single node, restricted container).
+void* mo_host_alloc_interleaved(size_t bytes) {
+#if defined(__linux__) && defined(SYS_set_mempolicy)
+  unsigned long mask = 0;
+  if (FILE* f = std::fopen("/sys/devices/system/node/online", "r")) {  // e.g. "0-1" or "0"
+    int lo = 0, hi = -1;
+    const int got = std::fscanf(f, "%d-%d", &lo, &hi);
+    std::fclose(f);
+    if (got == 1) hi = lo;
+    for (int i = lo; i <= hi && i < 64 && got >= 1; ++i) mask |= 1UL << i;
+  }
+  const bool multi = (mask & (mask - 1)) != 0;
+  const bool set = multi && syscall(SYS_set_mempolicy, 3 /* MPOL_INTERLEAVE */, &mask, sizeof(mask) * 8 + 1) == 0;
+  void* p = mo_host_alloc(bytes);
+  if (p && set) std::memset(p, 0, bytes);  // touch under the policy (cudaHostAlloc normally populates; this makes sure)
+  if (set) syscall(SYS_set_mempolicy, 0 /* MPOL_DEFAULT */, nullptr, 0);
+  return p;
+#else
+  return mo_host_alloc(bytes);
+#endif
 }
 
 int mo_qp_ip_solve_batch_host(const mo_qp_batch* problems, const mo_qp_params* params, const mo_qp_out* out,

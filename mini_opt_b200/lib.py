@@ -21,7 +21,7 @@ LIB_PATH = Path(os.environ.get("MINI_OPT_B200_LIB", PKG / "libminiopt_b200.so"))
 EXPORTS = [
     "mo_qp_params_default", "mo_qp_vars_stride", "mo_qp_ip_solve_batch", "mo_qp_ip_solve_batch_host", "mo_qp_ip_solve_batch_host_multi",
     "mo_qp_ip_newton_step_batch", "mo_qp_nullspace_solve_batch", "mo_qp_nullspace_solve_batch_noalloc", "mo_qp_nullspace_solve_batch_host", "mo_qp_kernel_variant", "mo_kernel_launch_count", "mo_last_error_string",
-    "mo_abi_version", "mo_host_alloc", "mo_host_free", "mo_measure_fp64_peak", "mo_measure_dmma_peak", "mo_nls_family_dims", "mo_nls_solve_family_batch", "mo_debug_set_tma", "mo_debug_set_tpp_async", "mo_debug_set_dm_kernel", "mo_debug_set_wd_lock", "mo_debug_set_ik_warps", "mo_debug_set_ik_sync",
+    "mo_abi_version", "mo_host_alloc", "mo_host_alloc_interleaved", "mo_host_free", "mo_measure_fp64_peak", "mo_measure_dmma_peak", "mo_nls_family_dims", "mo_nls_solve_family_batch", "mo_debug_set_tma", "mo_debug_set_tpp_async", "mo_debug_set_dm_kernel", "mo_debug_set_wd_lock", "mo_debug_set_ik_warps", "mo_debug_set_ik_sync",
     "mo_nls_params_default", "mo_nls_linearize_batch", "mo_chain_fk_batch", "mo_nls_solve_chain_ik_batch",
 ]
 
@@ -107,6 +107,8 @@ def load():
     lib.mo_nls_solve_chain_ik_batch.argtypes = [C.POINTER(abi.MoChainIkBatch), C.POINTER(abi.MoNlsParams),
                                                 C.POINTER(abi.MoNlsOut), C.c_int, C.c_void_p]
     lib.mo_nls_solve_chain_ik_batch.restype = C.c_int
+    lib.mo_host_alloc_interleaved.argtypes = [C.c_size_t]
+    lib.mo_host_alloc_interleaved.restype = C.c_void_p
     lib.mo_nls_family_dims.argtypes = [C.c_int32] + [C.POINTER(C.c_int32)] * 3
     lib.mo_nls_family_dims.restype = C.c_int
     lib.mo_nls_solve_family_batch.argtypes = [C.POINTER(abi.MoNlsFamilyBatch), C.POINTER(abi.MoNlsParams),

@@ -14,17 +14,22 @@ ap.add_argument("--devices", default="0,1")
 ap.add_argument("--n", type=int, default=8)
 ap.add_argument("--k", type=int, default=2)
 ap.add_argument("--per-gpu", type=int, default=1 << 20)
+ap.add_argument("--interleave", type=int, default=1, help="pinned buffers interleaved over the NUMA nodes (multi-device runs)")
 a = ap.parse_args()
 devs = [int(d) for d in a.devices.split(",")]
 L = lib.load()
 n, k, m = a.n, a.k, 2 * a.n
-res = {"n": n, "k": k, "per_gpu": a.per_gpu, "runs": []}
+res = {"n": n, "k": k, "per_gpu": a.per_gpu, "interleave": a.interleave, "runs": []}
+try:
+    res["numa_nodes_online"] = open("/sys/devices/system/node/online").read().strip()
+except OSError:
+    pass
 for nd in sorted({1, len(devs)}):
     B = a.per_gpu * nd
     host = synth.box_qp_batch_numpy(n, k, B, seed=1234, explicit_constraints=False)
     keep = []
     def pin(x):
-        v, p = bench.pinned_copy(L, x); keep.append(p); return v
+        v, p = bench.pinned_copy(L, x, interleaved=bool(a.interleave) and nd > 1); keep.append(p); return v
     harrs = abi.QPBatchArrays(n=n, k=k, m=m, batch=B, G=pin(qp.pack_lower(host.G)), c=pin(host.c), A_eq=pin(host.A_eq), b_eq=pin(host.b_eq),
                               ineq_b=pin(np.ascontiguousarray(host.ineq_b[0])),
                               flags=host.flags | abi.MO_QP_FLAG_PACKED_G | abi.MO_QP_FLAG_UNIFORM_BOX)
