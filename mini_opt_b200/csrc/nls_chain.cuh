@@ -77,6 +77,7 @@ struct ChainWork {
   int links, n;
   double* pose;    // [links][7] copy of link_pose
   double* base;    // [links][3] rotation_xyz of the ActuatorLink constructor (transform_chains.cc:107-122)
+  double* hsc;     // [links][6] (sin, cos) of base / 2 per axis: the half-angle factors of the axes that are NOT parameters
   double* lq;      // [links][4] link rotations at the current parameters
   double* lt;      // [links][3] link translations
   double* lD;      // [links][9] d(right tangent)/d(euler xyz)
@@ -92,7 +93,7 @@ struct ChainWork {
 };
 
 __host__ __device__ inline size_t chain_smem_doubles(int links, int n) {
-  size_t d = (size_t)links * (7 + 3 + 4 + 3 + 9) + (size_t)(links + 1) * (4 + 3 + 9) + 7 * (size_t)n;
+  size_t d = (size_t)links * (7 + 3 + 6 + 4 + 3 + 9) + (size_t)(links + 1) * (4 + 3 + 9) + 7 * (size_t)n;
   d += (size_t)links / 2 + 1;           // pos
   d += ((size_t)links * 6 + 7) / 8 + 1;  // mask
   d += 1;                               // have_cache
@@ -103,6 +104,7 @@ __device__ inline double* chain_carve(ChainWork& C, double* q, int links, int n)
   C.links = links; C.n = n;
   C.pose = q; q += links * 7;
   C.base = q; q += links * 3;
+  C.hsc = q; q += links * 6;
   C.lq = q; q += links * 4;
   C.lt = q; q += links * 3;
   C.lD = q; q += links * 9;
@@ -139,6 +141,9 @@ __device__ inline void chain_setup(ChainWork& C, const ChainArgs& a) {
     C.base[3 * i] = -atan2(2 * (y * z + x * w), 1 - 2 * (x * x + y * y));
     C.base[3 * i + 1] = -asin(fmax(fmin(1., -2 * (x * z - y * w)), -1.));
     C.base[3 * i + 2] = -atan2(2 * (x * y + z * w), 1 - 2 * (y * y + z * z));
+    // constant axes: the same sincos(angle / 2) chain_update would evaluate at every call (bit-identical, evaluated once)
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) sincos(C.base[3 * i + ax] / 2, &C.hsc[6 * i + 2 * ax], &C.hsc[6 * i + 2 * ax + 1]);
   }
   for (int e = lane; e < 3 * C.n; e += 32) { C.rotD[e] = 0.0; C.transD[e] = 0.0; }
   __syncwarp();
@@ -168,10 +173,12 @@ __device__ inline void chain_update(ChainWork& C, const double* params) {
     Quat q;
     double* D = C.lD + 9 * i;
     if (rot) {
-      double s_hx, c_hx, s_hy, c_hy, s_hz, c_hz;
-      sincos(pu[0] / 2, &s_hx, &c_hx);
-      sincos(pu[1] / 2, &s_hy, &c_hy);
-      sincos(pu[2] / 2, &s_hz, &c_hz);
+      // an axis that is a parameter moves; the others keep the half-angle factors computed in chain_setup
+      const double* H = C.hsc + 6 * i;
+      double s_hx = H[0], c_hx = H[1], s_hy = H[2], c_hy = H[3], s_hz = H[4], c_hz = H[5];
+      if (act[0]) sincos(pu[0] / 2, &s_hx, &c_hx);
+      if (act[1]) sincos(pu[1] / 2, &s_hy, &c_hy);
+      if (act[2]) sincos(pu[2] / 2, &s_hz, &c_hz);
       const double cy = 2 * c_hy * c_hy - 1, sy = 2 * c_hy * s_hy;
       const double cz = 2 * c_hz * c_hz - 1, sz = 2 * c_hz * s_hz;
       q.w = c_hx * c_hy * c_hz - s_hx * s_hy * s_hz;
