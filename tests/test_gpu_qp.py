@@ -244,6 +244,31 @@ def test_nonpositive_slack_status(dev, oracle, n, k, explicit, variant):
     assert (out.status[good] == ref.status[good]).mean() >= 0.97
 
 
+@pytest.mark.parametrize("n,k", [(8, 2), (4, 1)])
+@pytest.mark.parametrize("B", [1, 33, 1025, 37889])
+def test_tpp_refill_schedules_agree(dev, n, k, B):
+    """The cp.async refill of the thread-per-problem kernel (issued mid-round, lanes join one round later) and the round-1
+    register refill (mo_debug_set_tpp_async) must give bit-identical outputs, also for batches smaller than a warp, one past
+    a warp, and one past the resident thread slots."""
+    from mini_opt_b200 import lib
+    L = lib.load()
+    arrs = synth.box_qp_batch_numpy(n, k, B, seed=31, explicit_constraints=False)
+    assert lib.kernel_variant(n, k, 2 * n, arrs.flags) == "tpp"
+    prm = synth.solve_params()
+    outs = []
+    try:
+        for mode in (1, 0):
+            L.mo_debug_set_tpp_async(mode)
+            outs.append(gpu_solve(arrs, prm, dev))
+    finally:
+        L.mo_debug_set_tpp_async(1)
+    a, b = outs
+    assert np.array_equal(a.status, b.status) and np.array_equal(a.iters, b.iters)
+    assert np.array_equal(a.vars.view(np.int64), b.vars.view(np.int64))
+    assert np.array_equal(a.kkt_final.view(np.int64), b.kkt_final.view(np.int64))
+    assert (a.status >= 0).all() and (a.iters >= 1).all()
+
+
 def test_max_iterations_and_failures(dev, oracle):
     """MAX_ITERATIONS status, and per-problem failure codes instead of exceptions."""
     arrs = synth.box_qp_batch_numpy(8, 2, 500, seed=11, explicit_constraints=False)
