@@ -16,7 +16,7 @@ namespace mo {
 //   + software-pipelined, unrolled back substitution (PBS)          n=64 19.23   n=32 18.37   n=16 18.43   <- 16
 //   + look-ahead columns (LA: pivot chain under the gather DMMAs)    n=64 21.38   n=32 18.37   n=16 18.41
 // LA and PBS lose at n = 64 on instruction fetch: the kernel grows from 9.1K to 12.4K SASS instructions and
-// smsp stall no_instruction doubles (0.55 -> 1.12 cycles per issue, profiles/r02_wd64_la_ncu_summary.txt).
+// smsp stall no_instruction doubles (0.55 -> 1.12 cycles per issue, profiles/r02_wd_variants.txt).
 // (N, K, warps per problem, min CTAs per SM, look-ahead columns, pipelined back substitution)
 #ifndef MO_WD_SHAPES
 #define MO_WD_SHAPES(X) X(64, 16, 1, 7, false, false) X(32, 8, 1, 12, false, false) X(16, 8, 1, 16, false, true)
